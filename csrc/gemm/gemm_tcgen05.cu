@@ -1,0 +1,307 @@
+// K0: bf16 GEMM on the 5th-generation tensor cores.  D[M,N] (+)= op(A) * op(B), fp32 accumulation in
+// tensor memory.
+//
+//   * operands staged by TMA (cp.async.bulk.tensor, 128-byte swizzle) into a multi-stage smem ring
+//   * one elected thread issues tcgen05.mma (UMMA 128 x BN x 16, kind::f16) per k-slice
+//   * accumulators double-buffered in TMEM (2 x BN columns) so the epilogue of tile i overlaps the
+//     main loop of tile i+1
+//   * persistent CTAs (one per SM) walk the tile list; warp roles: 0 = TMA producer, 1 = MMA issuer
+//     (+ TMEM alloc), 2..5 = epilogue (tcgen05.ld -> convert -> global)
+//
+// Operand layouts (both operands independently):
+//   K-major  : A is [M,K] row-major (K contiguous) / B is [N,K] row-major   (torch Linear weight)
+//   MN-major : A is stored [K,M] row-major (M contiguous) / B is stored [K,N] row-major
+// which covers forward (x Wt), dgrad (dy W) and wgrad (dyT x) without any transposes in HBM.
+//
+// Reference: none — every GEMM in the reference is a cuBLAS call made by HF modules behind
+// `self.model(**batch)` (reference llmctl/runtime/engine.py:284) and `torch.matmul`
+// (reference llmctl/cli/commands/hw.py:317-337, llmctl/plugins/autotuning.py:89-114).
+// Baseline to beat: cuBLASLt bf16 (MEASURED_PEAKS.json).
+#include "../common/ptx.cuh"
+#include "../common/tma_host.h"
+#include "../common/util.cuh"
+
+namespace llmctl {
+using namespace ptx;
+
+constexpr int kBM = 128;
+constexpr int kBK = 64;  // 64 bf16 = one 128-byte swizzle row
+constexpr int kGemmThreads = 192;
+
+template <int BN>
+struct GemmCfg {
+  static constexpr int kStages = (BN == 256) ? 4 : 6;
+  static constexpr int kABytes = kBM * kBK * 2;
+  static constexpr int kBBytes = BN * kBK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024;  // + alignment slack
+  static constexpr int kTmemCols = 2 * BN;
+};
+
+// Epilogue modes
+enum : int { kEpiStore = 0, kEpiAccumulate = 1 };
+
+template <int BN, bool A_MN, bool B_MN, typename OutT>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    OutT* __restrict__ C, long long ldc, int M, int N, int K, int beta) {
+  using Cfg = GemmCfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint64_t bar_full[Cfg::kStages];
+  __shared__ uint64_t bar_empty[Cfg::kStages];
+  __shared__ uint64_t bar_tfull[2];
+  __shared__ uint64_t bar_tempty[2];
+  __shared__ uint32_t tmem_base_smem;
+
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem = smem_raw + (smem_base - smem_u32(smem_raw));
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  const int num_m = (M + kBM - 1) / kBM;
+  const int num_n = (N + BN - 1) / BN;
+  const int num_tiles = num_m * num_n;
+  const int num_kb = (K + kBK - 1) / kBK;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < Cfg::kStages; ++i) {
+      mbar_init(&bar_full[i], 1);
+      mbar_init(&bar_empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&bar_tfull[i], 1);
+      mbar_init(&bar_tempty[i], 4);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmA);
+    prefetch_tmap(&tmB);
+  }
+  if (warp == 1) tmem_alloc<1>(&tmem_base_smem, Cfg::kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_smem;
+
+  if (warp == 0) {
+    // ------------------------------ TMA producer ------------------------------
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int m0 = (tile % num_m) * kBM;
+        const int n0 = (tile / num_m) * BN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&bar_empty[stage], phase ^ 1u);
+          uint8_t* sA = smem + stage * Cfg::kStageBytes;
+          uint8_t* sB = sA + Cfg::kABytes;
+          mbar_expect_tx(&bar_full[stage], Cfg::kStageBytes);
+          const int k0 = kb * kBK;
+          if (!A_MN) {
+            tma_load_2d(sA, &tmA, &bar_full[stage], k0, m0);
+          } else {
+#pragma unroll
+            for (int g = 0; g < kBM / 64; ++g)
+              tma_load_2d(sA + g * 8192, &tmA, &bar_full[stage], m0 + g * 64, k0);
+          }
+          if (!B_MN) {
+            tma_load_2d(sB, &tmB, &bar_full[stage], k0, n0);
+          } else {
+#pragma unroll
+            for (int g = 0; g < BN / 64; ++g)
+              tma_load_2d(sB + g * 8192, &tmB, &bar_full[stage], n0 + g * 64, k0);
+          }
+          if (++stage == Cfg::kStages) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------ MMA issuer ------------------------------
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(kBM, BN, A_MN ? 1u : 0u, B_MN ? 1u : 0u);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t aphase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        mbar_wait(&bar_tempty[acc], aphase ^ 1u);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * BN);
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&bar_full[stage], phase);
+          tc_fence_after();
+          const uint32_t a_addr = smem_base + stage * Cfg::kStageBytes;
+          const uint32_t b_addr = a_addr + Cfg::kABytes;
+#pragma unroll
+          for (int k = 0; k < kBK / 16; ++k) {
+            const uint64_t da = A_MN ? make_smem_desc(a_addr + k * 2048, 8192, 1024, 2)
+                                     : make_smem_desc(a_addr + k * 32, 16, 1024, 2);
+            const uint64_t db = B_MN ? make_smem_desc(b_addr + k * 2048, 8192, 1024, 2)
+                                     : make_smem_desc(b_addr + k * 32, 16, 1024, 2);
+            umma_ss<1>(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+          umma_commit<1>(&bar_empty[stage]);  // frees the smem slot once these MMAs retire
+          if (++stage == Cfg::kStages) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+        umma_commit<1>(&bar_tfull[acc]);  // accumulator complete -> epilogue
+        acc ^= 1;
+        if (acc == 0) aphase ^= 1u;
+      }
+    }
+  } else {
+    // ------------------------------ epilogue (4 warps) ------------------------------
+    const int q = warp & 3;  // TMEM lane quadrant this warp may access
+    int acc = 0;
+    uint32_t aphase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int m0 = (tile % num_m) * kBM;
+      const int n0 = (tile / num_m) * BN;
+      mbar_wait(&bar_tfull[acc], aphase);
+      tc_fence_after();
+      const int row = m0 + q * 32 + lane;
+      const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) +
+                             static_cast<uint32_t>(acc * BN);
+      OutT* crow = C + static_cast<long long>(row) * ldc + n0;
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_x32(t_row + c * 32, r);
+        tmem_ld_wait();
+        if (row < M) {
+          if constexpr (sizeof(OutT) == 2) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const int col = n0 + c * 32 + j * 8;
+              if (col < N) {
+                float f[8];
+#pragma unroll
+                for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(r[j * 8 + e]);
+                __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(crow) + c * 32 + j * 8;
+                if (beta) {
+                  float old[8];
+                  unpack8(load8(dst), old);
+#pragma unroll
+                  for (int e = 0; e < 8; ++e) f[e] += old[e];
+                }
+                store8(dst, pack8(f));
+              }
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const int col = n0 + c * 32 + j * 4;
+              if (col < N) {
+                float4 v = make_float4(__uint_as_float(r[j * 4]), __uint_as_float(r[j * 4 + 1]),
+                                       __uint_as_float(r[j * 4 + 2]), __uint_as_float(r[j * 4 + 3]));
+                float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(crow) + c * 32 + j * 4);
+                if (beta) {
+                  const float4 o = *dst;
+                  v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
+                }
+                *dst = v;
+              }
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&bar_tempty[acc]);
+      acc ^= 1;
+      if (acc == 0) aphase ^= 1u;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<1>(tmem_base, Cfg::kTmemCols);
+  }
+}
+
+static int g_num_sms = 0;
+static int num_sms() {
+  if (g_num_sms == 0) {
+    int dev = 0, n = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess &&
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0)
+      g_num_sms = n;
+    else
+      g_num_sms = kNumSMs;
+  }
+  return g_num_sms;
+}
+
+template <int BN, bool A_MN, bool B_MN, typename OutT>
+static int launch_gemm(const void* A, const void* B, void* C, int M, int N, int K, long long lda,
+                       long long ldb, long long ldc, int beta, int max_ctas, cudaStream_t s) {
+  using Cfg = GemmCfg<BN>;
+  CUtensorMap tmA, tmB;
+  int rc;
+  if (!A_MN) rc = get_tmap_2d_bf16(&tmA, A, M, K, lda, kBM, kBK, 1);
+  else rc = get_tmap_2d_bf16(&tmA, A, K, M, lda, kBK, 64, 1);
+  if (rc) return rc;
+  if (!B_MN) rc = get_tmap_2d_bf16(&tmB, B, N, K, ldb, BN, kBK, 1);
+  else rc = get_tmap_2d_bf16(&tmB, B, K, N, ldb, kBK, 64, 1);
+  if (rc) return rc;
+  auto kern = gemm_tcgen05_kernel<BN, A_MN, B_MN, OutT>;
+  LLMCTL_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    Cfg::kSmemBytes));
+  const int tiles = ((M + kBM - 1) / kBM) * ((N + BN - 1) / BN);
+  int grid = num_sms();
+  if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
+  if (tiles < grid) grid = tiles;
+  kern<<<grid, kGemmThreads, Cfg::kSmemBytes, s>>>(tmA, tmB, (OutT*)C, ldc, M, N, K, beta);
+  LLMCTL_RETURN_LAST();
+}
+
+template <int BN, typename OutT>
+static int dispatch_layout(int a_mn, int b_mn, const void* A, const void* B, void* C, int M, int N,
+                           int K, long long lda, long long ldb, long long ldc, int beta,
+                           int max_ctas, cudaStream_t s) {
+  if (!a_mn && !b_mn) return launch_gemm<BN, false, false, OutT>(A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s);
+  if (!a_mn && b_mn) return launch_gemm<BN, false, true, OutT>(A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s);
+  if (a_mn && !b_mn) return launch_gemm<BN, true, false, OutT>(A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s);
+  return launch_gemm<BN, true, true, OutT>(A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s);
+}
+
+}  // namespace llmctl
+
+using namespace llmctl;
+
+// D[M,N] = op(A) op(B) (+ D if beta).  a_mn / b_mn select the operand storage (see file header).
+// out_fp32: D is fp32 (else bf16).  tile_n: 0 = auto, 128 or 256.  max_ctas: 0 = all SMs
+// (a smaller value leaves SMs free for a concurrent communication kernel).
+LLMCTL_API int llmctl_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K,
+                                long long lda, long long ldb, long long ldc, int a_mn, int b_mn,
+                                int out_fp32, int beta, int tile_n, int max_ctas, void* stream) {
+  LLMCTL_REQUIRE(M > 0 && N > 0 && K > 0);
+  LLMCTL_REQUIRE(lda % 8 == 0 && ldb % 8 == 0 && N % 8 == 0);
+  LLMCTL_REQUIRE((reinterpret_cast<uintptr_t>(A) & 15) == 0 && (reinterpret_cast<uintptr_t>(B) & 15) == 0 &&
+                 (reinterpret_cast<uintptr_t>(C) & 15) == 0);
+  LLMCTL_REQUIRE(out_fp32 ? (ldc % 4 == 0) : (ldc % 8 == 0));
+  cudaStream_t s = (cudaStream_t)stream;
+  int bn = tile_n;
+  if (bn != 128 && bn != 256) {
+    const int sms = num_sms();
+    const long long t256 = static_cast<long long>((M + 127) / 128) * ((N + 255) / 256);
+    const long long t128 = static_cast<long long>((M + 127) / 128) * ((N + 127) / 128);
+    const double c256 = static_cast<double>((t256 + sms - 1) / sms) * 2.0;
+    const double c128 = static_cast<double>((t128 + sms - 1) / sms) * 1.12;
+    bn = (c128 < c256) ? 128 : 256;
+  }
+  if (bn == 256) {
+    if (out_fp32) return dispatch_layout<256, float>(a_mn, b_mn, A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s);
+    return dispatch_layout<256, __nv_bfloat16>(a_mn, b_mn, A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s);
+  }
+  if (out_fp32) return dispatch_layout<128, float>(a_mn, b_mn, A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s);
+  return dispatch_layout<128, __nv_bfloat16>(a_mn, b_mn, A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s);
+}

@@ -1,0 +1,422 @@
+"""Data parallelism and ZeRO-1/2/3 over flat per-unit buffers.
+
+The model is cut into *units* (embedding, each transformer block, final norm, LM head).  Each unit owns
+
+* ``flat_param``  — all its bf16 parameters as views of one buffer (ZeRO-3: materialised only while the
+  unit is executing; the persistent copy is the rank's shard),
+* ``flat_grad``   — the gradient bucket the backward GEMMs write into directly (``param.main_grad``
+  views; see ``ops.functional._LinearFn``), reduced as soon as the unit's last gradient lands so the
+  collective overlaps the rest of backward (ZeRO-2/3: freed right after the reduce-scatter),
+* ``shard state`` — fp32 master weights + Adam moments for this rank's ``1/dp`` slice.
+
+Stage semantics
+    0  DP: gradient all-reduce, every rank holds full optimizer state.
+    1  optimizer state sharded; gradients reduce-scattered; parameters all-gathered after the step.
+    2  + gradient buckets are transient (only the reduced shard is kept).
+    3  + parameters sharded; all-gather before a unit's forward / backward, released afterwards.
+
+On CUDA the reduce-scatter + cast/scale + AdamW of a unit is the fused K7 kernel and the ZeRO-3 gather is K8
+(``comms/fused.py``); the torch.distributed calls here are the baseline transport and the CPU/gloo path.
+
+Reference: ZeRO exists only as the integer ``zero_stage`` (reference llmctl/cli/commands/plan.py:83-86,
+121-123,144) and an unused ``deepspeed`` import (reference llmctl/runtime/engine.py:25); DP is whatever
+``accelerator.prepare`` wraps (engine.py:265-267).
+"""
+from __future__ import annotations
+
+import math
+from typing import Callable, Dict, Iterable, List, Optional, Sequence
+
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+
+from ..comms.mesh import ParallelState, get_state
+from ..ops import optim as fused_optim
+
+_ALIGN = 128  # elements; keeps every parameter view 256-byte aligned (TMA needs 16)
+
+
+def _round_up(x: int, m: int) -> int:
+    return (x + m - 1) // m * m
+
+
+class ParamUnit:
+    """One reduction / gather bucket."""
+
+    def __init__(self, name: str, module: nn.Module, st: ParallelState, zero_stage: int, grad_dtype: torch.dtype):
+        self.name, self.module, self.st = name, module, st
+        self.zero_stage = zero_stage
+        self.grad_dtype = grad_dtype
+        params = [p for p in module.parameters() if p.requires_grad]
+        # replicated-over-TP parameters first so they form one contiguous segment
+        self.params: List[nn.Parameter] = sorted(params, key=lambda p: 0 if not hasattr(p, "tp_shard_dim") else 1)
+        self.dtype = self.params[0].dtype
+        self.device = self.params[0].device
+        self.shapes = [p.shape for p in self.params]
+        self.offsets: List[int] = []
+        off = 0
+        self.replicated_numel = 0
+        for p in self.params:
+            self.offsets.append(off)
+            off += _round_up(p.numel(), _ALIGN)
+            if not hasattr(p, "tp_shard_dim"):
+                self.replicated_numel = off
+        self.dp = st.dp
+        self.numel = _round_up(off, _ALIGN * self.dp)
+        self.shard_numel = self.numel // self.dp
+        self.shard_lo = st.dp_rank * self.shard_numel
+        self.shard_hi = self.shard_lo + self.shard_numel
+
+        # ---- parameters -> flat buffer -------------------------------------------------------
+        flat = torch.zeros(self.numel, dtype=self.dtype, device=self.device)
+        for p, o in zip(self.params, self.offsets):
+            flat[o:o + p.numel()].copy_(p.data.reshape(-1))
+        self.flat_param: Optional[torch.Tensor] = flat
+        self.param_shard: Optional[torch.Tensor] = None
+        self._bind_params(flat)
+        sharded_state = zero_stage >= 1 and self.dp > 1
+        lo, hi = (self.shard_lo, self.shard_hi) if sharded_state else (0, self.numel)
+        self.state_lo, self.state_hi = lo, hi
+        self.master = flat[lo:hi].float().clone()
+        self.exp_avg = torch.zeros_like(self.master)
+        self.exp_avg_sq = torch.zeros_like(self.master)
+        if zero_stage >= 3 and self.dp > 1:
+            self.param_shard = flat[self.shard_lo:self.shard_hi].clone()
+            self._release_params()
+
+        # ---- gradients ---------------------------------------------------------------------------
+        self.flat_grad: Optional[torch.Tensor] = None
+        self.grad_shard: Optional[torch.Tensor] = None     # reduced gradients for the state slice
+        self._pending = 0
+        self._fresh = True            # first micro-batch of the step: write (beta=0), later accumulate
+        self._work = None
+        self._on_ready: Optional[Callable[["ParamUnit"], None]] = None
+        for p in self.params:
+            p._zero_unit = self
+            p._grad_ready_cb = self._param_grad_ready
+            p.register_post_accumulate_grad_hook(self._autograd_hook)
+
+    # ------------------------------------------------------------------------------------------
+    def _bind_params(self, flat: torch.Tensor) -> None:
+        for p, o, shp in zip(self.params, self.offsets, self.shapes):
+            p.data = flat[o:o + shp.numel()].view(shp)
+
+    def _release_params(self) -> None:
+        self.flat_param = None
+        for p in self.params:
+            p.data = torch.empty(0, dtype=self.dtype, device=self.device)
+
+    @property
+    def params_resident(self) -> bool:
+        return self.flat_param is not None
+
+    def gather_params(self) -> None:
+        """ZeRO-3: materialise the full parameters from the shards (no-op if resident)."""
+        if self.flat_param is not None:
+            return
+        flat = torch.empty(self.numel, dtype=self.dtype, device=self.device)
+        dist.all_gather_into_tensor(flat, self.param_shard, group=self.st.dp_group)
+        self.flat_param = flat
+        self._bind_params(flat)
+
+    def release_params(self) -> None:
+        if self.zero_stage >= 3 and self.dp > 1 and self.flat_param is not None:
+            self._release_params()
+
+    # ---- gradient bucket -----------------------------------------------------------------------
+    def ensure_grad_bucket(self) -> None:
+        if self.flat_grad is None:
+            self.flat_grad = torch.empty(self.numel, dtype=self.grad_dtype, device=self.device)
+            self._bucket_fresh = True
+            self._pending = len(self.params)
+            for p, o, shp in zip(self.params, self.offsets, self.shapes):
+                p.main_grad = self.flat_grad[o:o + shp.numel()].view(shp)
+                p._main_grad_fresh = True
+        elif self._pending == 0:
+            self._pending = len(self.params)
+
+    def _autograd_hook(self, p: nn.Parameter) -> None:
+        """Gradient produced by autograd (norm weights, embeddings, baseline GEMMs): fold into the bucket."""
+        if p.grad is None:
+            return
+        self.ensure_grad_bucket()
+        g = p.grad
+        if getattr(p, "_main_grad_fresh", True):
+            p.main_grad.copy_(g)
+            p._main_grad_fresh = False
+        else:
+            p.main_grad.add_(g)
+        p.grad = None
+        self._param_grad_ready(p)
+
+    def _param_grad_ready(self, p: nn.Parameter) -> None:
+        self._pending -= 1
+        if self._pending == 0 and self._on_ready is not None:
+            self._on_ready(self)
+
+
+class ZeroOptimizer:
+    """AdamW over ``ParamUnit``s with DP / ZeRO-1/2/3 gradient and parameter collectives."""
+
+    def __init__(self, model: nn.Module, *, lr: float = 2e-4, betas=(0.9, 0.95), eps: float = 1e-8,
+                 weight_decay: float = 0.1, zero_stage: int = 0, grad_clip: float = 1.0,
+                 grad_dtype: Optional[torch.dtype] = None, units: Optional[Sequence] = None,
+                 state: Optional[ParallelState] = None):
+        self.st = state or get_state()
+        self.model = model
+        self.lr, self.betas, self.eps, self.weight_decay = lr, betas, eps, weight_decay
+        self.grad_clip = grad_clip
+        self.zero_stage = zero_stage
+        self.step_count = 0
+        self.grad_accum_steps = 1
+        self._micro = 0
+        first = next(p for p in model.parameters() if p.requires_grad)
+        self.grad_dtype = grad_dtype or (torch.float32 if first.dtype == torch.float32 else torch.bfloat16)
+        named = units if units is not None else default_units(model)
+        self.units: List[ParamUnit] = []
+        for name, mod in named:
+            if any(p.requires_grad for p in mod.parameters()):
+                u = ParamUnit(name, mod, self.st, self.zero_stage, self.grad_dtype)
+                u._on_ready = self._unit_ready
+                self.units.append(u)
+        self._last_micro = True
+        self._norm_buf = None
+        self.last_grad_norm: Optional[torch.Tensor] = None
+        self._install_hooks()
+
+    # ---- hooks ---------------------------------------------------------------------------------
+    def _install_hooks(self) -> None:
+        for u in self.units:
+            u.module.register_full_backward_pre_hook(lambda m, g, u=u: self._pre_backward(u))
+            if self.zero_stage >= 3 and self.st.dp > 1:
+                u.module.register_forward_pre_hook(lambda m, a, u=u: u.gather_params())
+                u.module.register_forward_hook(lambda m, a, o, u=u: self._post_forward(u))
+
+    def _post_forward(self, u: ParamUnit) -> None:
+        # keep the parameters while a checkpointed recompute is inside backward (freed by _unit_ready)
+        if not torch.is_grad_enabled() or not getattr(self, "_in_backward", False):
+            u.release_params()
+
+    def _pre_backward(self, u: ParamUnit) -> None:
+        self._in_backward = True
+        if self.zero_stage >= 3 and self.st.dp > 1:
+            u.gather_params()
+        u.ensure_grad_bucket()
+
+    # ---- gradient reduction (fires from backward as each unit completes) ---------------------
+    def _unit_ready(self, u: ParamUnit) -> None:
+        if self.zero_stage >= 3:
+            u.release_params()
+        if not self._last_micro and self.zero_stage < 2:
+            return  # keep accumulating locally; reduce once on the last micro-batch
+        self._reduce_unit(u)
+
+    def _reduce_unit(self, u: ParamUnit) -> None:
+        st = self.st
+        g = u.flat_grad
+        if st.dp == 1:
+            u.grad_shard = g
+            return
+        if self.zero_stage == 0:
+            u._work = dist.all_reduce(g, group=st.dp_group, async_op=True)
+            u.grad_shard = g
+            return
+        out = torch.empty(u.shard_numel, dtype=g.dtype, device=g.device)
+        if dist.get_backend(st.dp_group) == "gloo":
+            dist.all_reduce(g, group=st.dp_group)
+            out.copy_(g[u.shard_lo:u.shard_hi])
+        else:
+            u._work = dist.reduce_scatter_tensor(out, g, group=st.dp_group, async_op=True)
+        if self.zero_stage >= 2:
+            # transient bucket: accumulate the reduced shard across micro-batches, drop the bucket
+            if u._work is not None:
+                u._work.wait()
+                u._work = None
+            if u.grad_shard is None or getattr(u, "_shard_fresh", True):
+                u.grad_shard = out if out.dtype == torch.float32 else out.float()
+                u._shard_fresh = False
+            else:
+                u.grad_shard.add_(out)
+            u.flat_grad = None
+            for p in u.params:
+                p.main_grad = None
+        else:
+            u.grad_shard = out
+
+    # ---- public API ----------------------------------------------------------------------------
+    def set_micro_batch(self, index: int, total: int) -> None:
+        """Tell the optimizer where we are inside gradient accumulation (controls when to reduce)."""
+        self._micro, self.grad_accum_steps = index, total
+        self._last_micro = index == total - 1
+
+    def zero_grad(self) -> None:
+        for u in self.units:
+            u.grad_shard = None
+            u._shard_fresh = True
+            if self.zero_stage >= 2 and self.st.dp > 1:
+                u.flat_grad = None
+            if u.flat_grad is not None:
+                for p in u.params:
+                    p._main_grad_fresh = True
+            u._pending = 0
+        for p in self.model.parameters():
+            p.grad = None
+
+    def _finish_reductions(self) -> None:
+        self._in_backward = False
+        for u in self.units:
+            if u.grad_shard is None and u.flat_grad is not None:
+                # unit never signalled (e.g. unused parameters): reduce what we have
+                for p in u.params:
+                    if getattr(p, "_main_grad_fresh", True) and p.main_grad is not None:
+                        p.main_grad.zero_()
+                        p._main_grad_fresh = False
+                self._reduce_unit(u)
+            if u._work is not None:
+                u._work.wait()
+                u._work = None
+
+    def _sync_replicated_grads(self) -> None:
+        """Sequence parallelism: norm weights see only a token shard per TP rank -> sum over TP."""
+        st = self.st
+        if st.tp == 1 or not st.sequence_parallel:
+            return
+        for u in self.units:
+            if u.replicated_numel == 0 or u.grad_shard is None:
+                continue
+            lo, hi = max(u.state_lo, 0), min(u.state_hi, u.replicated_numel)
+            if hi > lo:
+                seg = u.grad_shard[lo - u.state_lo:hi - u.state_lo]
+                dist.all_reduce(seg, group=st.tp_group)
+
+    def grad_norm_sq(self) -> torch.Tensor:
+        st = self.st
+        dev = self.units[0].device
+        total = torch.zeros(1, dtype=torch.float32, device=dev)
+        for u in self.units:
+            if u.grad_shard is None:
+                continue
+            g = u.grad_shard
+            rep_hi = min(u.state_hi, u.replicated_numel) - u.state_lo
+            if st.tp > 1 and rep_hi > 0:
+                # replicated parameters are counted once (by tp_rank 0)
+                if st.tp_rank == 0:
+                    fused_optim.sumsq(g[:rep_hi], total, accumulate=True)
+                if rep_hi < g.numel():
+                    fused_optim.sumsq(g[rep_hi:], total, accumulate=True)
+            else:
+                fused_optim.sumsq(g, total, accumulate=True)
+        if self.zero_stage == 0 or st.dp == 1:
+            pass  # every DP rank already holds the full reduced gradient
+        else:
+            dist.all_reduce(total, group=st.dp_group)
+        if st.tp > 1:
+            dist.all_reduce(total, group=st.tp_group)
+        if st.pp > 1:
+            dist.all_reduce(total, group=st.pp_group)
+        return total
+
+    def step(self, lr: Optional[float] = None) -> torch.Tensor:
+        """Finish gradient reduction, clip by global norm, AdamW on this rank's slice, re-publish parameters.
+        Returns the (device) gradient norm.  No host synchronisation happens here."""
+        st = self.st
+        lr = self.lr if lr is None else lr
+        self._finish_reductions()
+        self._sync_replicated_grads()
+        # losses are already divided by grad_accum_steps by the engine (loss_scale): only 1/dp is left
+        inv = 1.0 / st.dp
+        total = self.grad_norm_sq() * (inv * inv)
+        self.last_grad_norm = total.sqrt()
+        coef = fused_optim.clip_coefficient(total, self.grad_clip)
+        self.step_count += 1
+        for u in self.units:
+            if u.grad_shard is None:
+                continue
+            sharded = self.zero_stage >= 1 and st.dp > 1
+            if self.zero_stage >= 3 and st.dp > 1:
+                out = u.param_shard
+            elif u.flat_param is not None:
+                out = u.flat_param[u.state_lo:u.state_hi]
+            else:
+                out = None
+            fused_optim.adamw_step(u.master, u.exp_avg, u.exp_avg_sq, u.grad_shard, out, step=self.step_count,
+                                   lr=lr, beta1=self.betas[0], beta2=self.betas[1], eps=self.eps,
+                                   weight_decay=self.weight_decay, grad_scale=inv, scale_dev=coef)
+            if sharded and self.zero_stage < 3:
+                dist.all_gather_into_tensor(u.flat_param, u.flat_param[u.shard_lo:u.shard_hi].clone()
+                                            if dist.get_backend(st.dp_group) == "gloo"
+                                            else u.flat_param[u.shard_lo:u.shard_hi], group=st.dp_group)
+        self.zero_grad()
+        return self.last_grad_norm
+
+    # ---- state dict (per-rank shard; see io/checkpoint.py) -------------------------------------
+    def state_dict(self) -> Dict:
+        return {
+            "step": self.step_count,
+            "zero_stage": self.zero_stage,
+            "dp": self.st.dp,
+            "units": {u.name: {"master": u.master, "exp_avg": u.exp_avg, "exp_avg_sq": u.exp_avg_sq,
+                               "lo": u.state_lo, "hi": u.state_hi, "numel": u.numel} for u in self.units},
+        }
+
+    def load_state_dict(self, sd: Dict) -> None:
+        self.step_count = int(sd["step"])
+        for u in self.units:
+            s = sd["units"][u.name]
+            if (s["lo"], s["hi"]) != (u.state_lo, u.state_hi):
+                raise ValueError(f"optimizer shard layout changed for unit {u.name}; use the re-sharding loader")
+            u.master.copy_(s["master"])
+            u.exp_avg.copy_(s["exp_avg"])
+            u.exp_avg_sq.copy_(s["exp_avg_sq"])
+            self._publish(u)
+
+    def _publish(self, u: ParamUnit) -> None:
+        """Write master weights back into the bf16 parameters (after a load)."""
+        st = self.st
+        if self.zero_stage >= 3 and st.dp > 1:
+            u.param_shard.copy_(u.master)
+            return
+        u.flat_param[u.state_lo:u.state_hi].copy_(u.master)
+        if self.zero_stage >= 1 and st.dp > 1:
+            src = u.flat_param[u.shard_lo:u.shard_hi].clone()
+            dist.all_gather_into_tensor(u.flat_param, src, group=st.dp_group)
+
+    def full_params_context(self):
+        return _FullParams(self)
+
+
+class _FullParams:
+    """Context manager: ZeRO-3 parameters gathered for the duration (checkpoint save, eval, export)."""
+
+    def __init__(self, opt: ZeroOptimizer):
+        self.opt = opt
+
+    def __enter__(self):
+        for u in self.opt.units:
+            if self.opt.zero_stage >= 3 and self.opt.st.dp > 1:
+                u.gather_params()
+        return self
+
+    def __exit__(self, *exc):
+        for u in self.opt.units:
+            u.release_params()
+        return False
+
+
+def default_units(model: nn.Module):
+    """(name, module) buckets: embedding, each block, final norm, LM head."""
+    units = []
+    if hasattr(model, "embed"):
+        units.append(("embed", model.embed))
+    if hasattr(model, "blocks"):
+        lo = getattr(model, "layer_lo", 0)
+        for i, b in enumerate(model.blocks):
+            units.append((f"block{lo + i}", b))
+    if hasattr(model, "final_norm"):
+        units.append(("final_norm", model.final_norm))
+    if getattr(model, "lm_head", None) is not None:
+        units.append(("lm_head", model.lm_head))
+    if not units:
+        units = [("model", model)]
+    return units

@@ -1,0 +1,81 @@
+/* C ABI of libllmctl_b200.so — hand-written sm_100a kernels.
+ *
+ * Conventions
+ *   - every function returns a cudaError_t value as int (0 = success, 1 = invalid argument);
+ *   - all device pointers are raw addresses, bf16 unless stated; `stream` is a cudaStream_t;
+ *   - nothing here allocates device memory: outputs and scratch are passed in by the caller;
+ *   - launches are asynchronous on `stream`.
+ *
+ * The reference repository ships no native code; the "Reference:" notes name the
+ * library path the reference reaches for the same work.
+ */
+#ifndef LLMCTL_B200_H_
+#define LLMCTL_B200_H_
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- K3 norms.  Reference: ATen rms_norm/layer_norm inside HF modules (engine.py:284). ---- */
+/* h = x (+ residual); y = h * rsqrt(mean(h^2) + eps) * w.  h_out/residual/rstd may be NULL. */
+int llmctl_rmsnorm_fwd(const void* x, const void* residual, const void* w, void* h_out, void* y,
+                       float* rstd, int rows, int cols, float eps, void* stream);
+/* dx = d(norm)/dh (+ dres); dw (fp32) (+)= sum_rows dy * xhat.
+ * scratch: fp32 [scratch_rows * cols]; scratch_rows CTAs are used (1..rows). */
+int llmctl_rmsnorm_bwd(const void* dy, const void* h, const void* w, const float* rstd,
+                       const void* dres, void* dx, float* dw, float* scratch, int scratch_rows,
+                       int rows, int cols, int accumulate, void* stream);
+int llmctl_layernorm_fwd(const void* x, const void* residual, const void* w, const void* b,
+                         void* h_out, void* y, float* mean, float* rstd, int rows, int cols,
+                         float eps, void* stream);
+/* scratch: fp32 [2 * scratch_rows * cols] */
+int llmctl_layernorm_bwd(const void* dy, const void* h, const void* w, const float* mean,
+                         const float* rstd, const void* dres, void* dx, float* dw, float* db,
+                         float* scratch, int scratch_rows, int rows, int cols, int accumulate,
+                         void* stream);
+
+/* ---- K4 RoPE (rotate-half), in place; sign=+1 forward, -1 backward.  Reference: HF rotary. ---- */
+int llmctl_rope_inplace(void* x, long long row_stride, int n_tokens, int n_heads, int head_dim,
+                        const float* cos_t, const float* sin_t, const int* positions, int seq_len,
+                        float sign, void* stream);
+
+/* ---- K5 SwiGLU on packed [M, 2F] gate|up.  Reference: ATen silu + mul. ---- */
+int llmctl_swiglu_fwd(const void* gate_up, void* out, int M, int F, long long ld_gu, void* stream);
+int llmctl_swiglu_bwd(const void* dout, const void* gate_up, void* d_gate_up, int M, int F,
+                      long long ld_gu, void* stream);
+
+/* ---- K9 fused AdamW + grad-norm pieces.  Reference: torch.optim.AdamW (engine.py:230-235),
+ *      clip_grad_norm_ (engine.py:295-299). ---- */
+int llmctl_adamw_step(void* master, void* m, void* v, const void* grad, int grad_is_fp32,
+                      void* param_out, long long n, float lr, float beta1, float beta2, float eps,
+                      float weight_decay, float bias_corr1, float bias_corr2, float host_scale,
+                      const float* scale_dev, void* stream);
+/* out (+)= sum(x^2); scratch: fp32 [scratch_elems] partial sums (deterministic two-stage). */
+int llmctl_sumsq(const void* x, int is_fp32, long long n, float* scratch, int scratch_elems,
+                 float* out, int accumulate, void* stream);
+
+/* ---- K15 cross entropy (fused fwd+bwd, in-place gradient).  Reference: HF CrossEntropyLoss. ---- */
+int llmctl_cross_entropy_fwd_bwd(void* logits, long long ld, const long long* targets,
+                                 float* loss_per_row, float* lse_per_row, int rows, int V,
+                                 long long ignore_index, float host_scale, const float* scale_dev,
+                                 int write_grad, void* stream);
+int llmctl_cross_entropy_partial(const void* logits, long long ld, const long long* targets,
+                                 float* stats, int rows, int V_local, long long vocab_start,
+                                 void* stream);
+int llmctl_cross_entropy_finalize(void* logits, long long ld, const long long* targets,
+                                  const float* lse, int rows, int V_local, long long vocab_start,
+                                  long long ignore_index, float host_scale, const float* scale_dev,
+                                  void* stream);
+
+/* ---- K0 tcgen05/TMA GEMM.  Reference: cuBLAS via torch.matmul / nn.Linear. ----
+ * D[M,N] = op(A) op(B) (+ D if beta).  a_mn=0: A is [M,K] row-major; a_mn=1: A stored [K,M].
+ * b_mn=0: B is [N,K] row-major (Linear weight); b_mn=1: B stored [K,N].
+ * out_fp32: D fp32 else bf16.  tile_n: 0 auto | 128 | 256.  max_ctas: 0 = all SMs. */
+int llmctl_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, long long lda,
+                     long long ldb, long long ldc, int a_mn, int b_mn, int out_fp32, int beta,
+                     int tile_n, int max_ctas, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LLMCTL_B200_H_ */
