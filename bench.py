@@ -1,0 +1,251 @@
+#!/usr/bin/env python
+"""Headline benchmark: GPT-7B training throughput (tokens/s) on N B200s of one node.
+
+    python bench.py --gpus 1 --steps 8 --warmup 3
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+        bench.py --gpus N --steps K --warmup W
+    python bench.py --impl reference ...      # the unmodified reference from baseline/_ref (see baseline/)
+
+Metric / config follow BASELINE.json ("train tokens/sec, GPT-7B, 1/2/4/8 B200").  Workload shape mirrors the
+reference's own training step: micro-batch 8 sequences x 512 tokens per GPU (reference
+llmctl/runtime/engine.py:41 ``batch_size=8`` and :163 ``max_length=512``), AdamW(0.9, 0.95), global-norm
+clipping at 1.0, bf16 compute with fp32 master weights, synthetic tokens, random-init weights.  N>1 is data
+parallel with ZeRO-1 (weak scaling: per-GPU work fixed).
+
+Two numbers are reported:
+  value     device-timed (CUDA events, max over ranks) over exactly K steps with inputs already resident;
+  e2e.value the same K steps through the public API ``TrainingEngine.train_step()`` with, every step, the
+            H2D copy of that step's tokens from pinned host memory and a D2H read of the loss.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+if str(ROOT) not in sys.path:
+    sys.path.insert(0, str(ROOT))
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=8)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="native", choices=["native", "baseline", "reference"])
+    ap.add_argument("--model", default="gpt-7b")
+    ap.add_argument("--seq-len", type=int, default=512)
+    ap.add_argument("--micro-batch", type=int, default=8)
+    ap.add_argument("--zero-stage", type=int, default=None)
+    ap.add_argument("--tp", type=int, default=1)
+    ap.add_argument("--pp", type=int, default=1)
+    ap.add_argument("--sp", action="store_true")
+    ap.add_argument("--activation-checkpoint", default="none")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--gemm", default=None, help="override GEMM backend: native|cublas")
+    ap.add_argument("--attention", default=None, help="override attention backend: native|sdpa")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------------------
+# clocks (sampled DURING the timed region, per /opt/skills/guides/B200_PROFILING.md)
+# ------------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int = 0):
+        self.gpu, self.proc, self.lines = gpu_index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200", "-i", str(self.gpu)], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self._t = threading.Thread(target=self._read, daemon=True)
+            self._t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons, power = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2])); power.append(float(f[3]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "power_w_max": max(power),
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def run_native(args) -> dict:
+    import torch
+    import torch.distributed as dist
+    from llmctl_b200.models.config import resolve_model
+    from llmctl_b200.ops import functional as ops
+    from llmctl_b200.ops import native
+    from llmctl_b200.runtime.engine import TrainingEngine, create_training_config
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world} (launch with torchrun for N>1)"
+    dp = world // (args.tp * args.pp)
+    zero = args.zero_stage if args.zero_stage is not None else (1 if dp > 1 else 0)
+    import tempfile
+    tc = create_training_config(
+        model_name_or_path=args.model, output_dir=tempfile.mkdtemp(prefix="llmctl_bench_"),
+        batch_size=args.micro_batch, seq_len=args.seq_len, gradient_accumulation_steps=1, max_steps=10 ** 9,
+        learning_rate=2e-4, weight_decay=0.1, gradient_clipping=1.0, warmup_steps=0, scheduler="constant",
+        mixed_precision="bf16", tensor_parallel=args.tp, pipeline_parallel=args.pp, sequence_parallel=args.sp,
+        zero_stage=zero, activation_checkpoint=args.activation_checkpoint,
+        kernels="baseline" if args.impl == "baseline" else "native", eval_steps=0, save_steps=0,
+        logging_steps=10 ** 9, log_level="warning", metrics_jsonl=False)
+    eng = TrainingEngine(tc)
+    if args.gemm:
+        ops.kernel_config().gemm = args.gemm
+    if args.attention:
+        ops.kernel_config().attention = args.attention
+    st = eng.state
+    eng.load_model_and_tokenizer()
+    eng.prepare_datasets()
+    eng.setup_optimizer_and_scheduler()
+    dev = st.device
+    mcfg = eng.model_config
+    K, W = args.steps, args.warmup
+    tokens_per_step = args.micro_batch * args.seq_len * st.dp
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---------------- device-timed: inputs pre-staged on the device, no host sync inside ----------------
+    staged = [eng.train_dataloader.next_batch() for _ in range(min(K + W, 16))]
+    torch.cuda.synchronize()
+
+    def step_resident(i):
+        tok, tgt = staged[i % len(staged)]
+        eng.optimizer.set_micro_batch(0, 1)
+        loss = eng.model(tok, targets=tgt, loss_scale=1.0)
+        loss.backward()
+        eng.optimizer.step(2e-4)
+        return loss
+
+    for i in range(W):
+        step_resident(i)
+    barrier()
+    sampler = ClockSampler(st.local_rank) if st.rank == 0 else None
+    if sampler:
+        sampler.start()
+    launches0 = native.launch_count
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for i in range(K):
+        loss = step_resident(W + i)
+    ev1.record()
+    barrier()
+    launches = native.launch_count - launches0
+    clocks = sampler.stop() if sampler else {}
+    ms = torch.tensor([ev0.elapsed_time(ev1)], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_per_step = float(ms.item()) / K
+    value = tokens_per_step / (ms_per_step / 1e3)
+    final_loss = float(loss)
+
+    # ---------------- end to end through the public API: H2D every step + D2H loss read -----------------
+    e2e = None
+    if not args.no_e2e:
+        eng.train_dataloader.prefetch = False   # copy this step's inputs inside the timed region
+        for _ in range(2):
+            float(eng.train_step()["loss"])
+        barrier()
+        t0 = time.perf_counter()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(K):
+            out = eng.train_step()
+            _ = float(out["loss"])          # device -> host read of the step result
+        e1.record()
+        barrier()
+        wall_ms = (time.perf_counter() - t0) * 1e3
+        t = torch.tensor([max(e0.elapsed_time(e1), wall_ms)], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_ms = float(t.item()) / K
+        e2e = {"value": tokens_per_step / (e2e_ms / 1e3), "unit": "tokens/s", "ms_per_step": e2e_ms,
+               "h2d_bytes_per_step": args.micro_batch * (args.seq_len + 1) * 8,
+               "d2h_bytes_per_step": 4, "api": "llmctl_b200.runtime.engine.TrainingEngine.train_step"}
+
+    par = f"dp{st.dp}" + (f"-zero{zero}" if st.dp > 1 else "") + (f"-tp{st.tp}" if st.tp > 1 else "") + \
+          (f"-pp{st.pp}" if st.pp > 1 else "") + ("-sp" if st.sequence_parallel else "")
+    flops_tok = mcfg.flops_per_token(args.seq_len)
+    kc = ops.kernel_config()
+    res = {
+        "metric": "train tokens/sec (GPT-7B)", "value": value, "unit": "tokens/s", "n_gpus": world, "steps": K,
+        "warmup": W, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "bf16", "data": "synthetic tokens, random-init weights",
+        "impl": args.impl,
+        "config": {"model": mcfg.name, "params": mcfg.num_parameters(), "global_batch": args.micro_batch * st.dp,
+                   "micro_batch": args.micro_batch, "seq_len": args.seq_len, "parallelism": par,
+                   "optimizer": "AdamW fp32 master + moments, clip 1.0", "activation_checkpoint": args.activation_checkpoint,
+                   "l2": "inputs larger than L2: every step streams >100 GB of weights/optimizer state (L2 = 126 MB)",
+                   "kernels": {"gemm": kc.gemm, "attention": kc.attention, "elementwise": kc.elementwise,
+                               "optimizer": kc.optimizer}},
+        "model_tflops_per_gpu": value * flops_tok / world / 1e12,
+        "final_loss": final_loss, "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
+    }
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return res if st.rank == 0 else None
+
+
+def run_reference(args) -> dict:
+    sys.path.insert(0, str(ROOT / "baseline"))
+    try:
+        from reference_arm import run as ref_run
+    except Exception as e:  # noqa: BLE001
+        return {"impl": "reference", "unavailable": f"baseline harness import failed: {type(e).__name__}: {e}"[:300]}
+    return ref_run(args)
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        res = run_reference(args)
+    else:
+        res = run_native(args)
+    if res is not None:
+        print(json.dumps(res), flush=True)
+
+
+if __name__ == "__main__":
+    main()

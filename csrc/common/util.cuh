@@ -8,6 +8,10 @@
 
 #define LLMCTL_API extern "C" __attribute__((visibility("default")))
 
+// Clear any stale (non-sticky) error left behind by another library on this thread, so that the status
+// we return describes *our* launch only.
+#define LLMCTL_BEGIN() (void)cudaGetLastError()
+
 // Every entry point returns a cudaError_t cast to int (0 == success).
 #define LLMCTL_RETURN_LAST()               \
   do {                                     \

@@ -283,6 +283,7 @@ using namespace llmctl;
 LLMCTL_API int llmctl_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K,
                                 long long lda, long long ldb, long long ldc, int a_mn, int b_mn,
                                 int out_fp32, int beta, int tile_n, int max_ctas, void* stream) {
+  LLMCTL_BEGIN();
   LLMCTL_REQUIRE(M > 0 && N > 0 && K > 0);
   LLMCTL_REQUIRE(lda % 8 == 0 && ldb % 8 == 0 && N % 8 == 0);
   LLMCTL_REQUIRE((reinterpret_cast<uintptr_t>(A) & 15) == 0 && (reinterpret_cast<uintptr_t>(B) & 15) == 0 &&

@@ -204,6 +204,7 @@ LLMCTL_API int llmctl_cross_entropy_fwd_bwd(void* logits, long long ld, const lo
                                             float* loss_per_row, float* lse_per_row, int rows,
                                             int V, long long ignore_index, float host_scale,
                                             const float* scale_dev, int write_grad, void* stream) {
+  LLMCTL_BEGIN();
   LLMCTL_REQUIRE(V % 8 == 0 && ld % 8 == 0 && ld >= V);
   if (rows == 0) return 0;
   cudaStream_t s = (cudaStream_t)stream;
@@ -227,6 +228,7 @@ LLMCTL_API int llmctl_cross_entropy_fwd_bwd(void* logits, long long ld, const lo
 LLMCTL_API int llmctl_cross_entropy_partial(const void* logits, long long ld,
                                             const long long* targets, float* stats, int rows,
                                             int V_local, long long vocab_start, void* stream) {
+  LLMCTL_BEGIN();
   LLMCTL_REQUIRE(V_local % 8 == 0 && ld % 8 == 0);
   if (rows == 0) return 0;
   ce_partial_kernel<<<rows, kCEThreads, 0, (cudaStream_t)stream>>>(
@@ -239,6 +241,7 @@ LLMCTL_API int llmctl_cross_entropy_finalize(void* logits, long long ld, const l
                                              long long vocab_start, long long ignore_index,
                                              float host_scale, const float* scale_dev,
                                              void* stream) {
+  LLMCTL_BEGIN();
   LLMCTL_REQUIRE(V_local % 8 == 0 && ld % 8 == 0);
   if (rows == 0) return 0;
   ce_finalize_kernel<<<rows, kCEThreads, 0, (cudaStream_t)stream>>>(

@@ -272,6 +272,7 @@ using namespace llmctl;
 LLMCTL_API int llmctl_rmsnorm_fwd(const void* x, const void* residual, const void* w, void* h_out,
                                   void* y, float* rstd, int rows, int cols, float eps,
                                   void* stream) {
+  LLMCTL_BEGIN();
   return launch_fwd<false>(x, residual, w, nullptr, h_out, y, nullptr, rstd, rows, cols, eps,
                            (cudaStream_t)stream);
 }
@@ -279,12 +280,14 @@ LLMCTL_API int llmctl_rmsnorm_bwd(const void* dy, const void* h, const void* w, 
                                   const void* dres, void* dx, float* dw, float* scratch,
                                   int scratch_rows, int rows, int cols, int accumulate,
                                   void* stream) {
+  LLMCTL_BEGIN();
   return launch_bwd<false>(dy, h, w, nullptr, rstd, dres, dx, dw, nullptr, scratch, scratch_rows,
                            rows, cols, accumulate, (cudaStream_t)stream);
 }
 LLMCTL_API int llmctl_layernorm_fwd(const void* x, const void* residual, const void* w,
                                     const void* b, void* h_out, void* y, float* mean, float* rstd,
                                     int rows, int cols, float eps, void* stream) {
+  LLMCTL_BEGIN();
   return launch_fwd<true>(x, residual, w, b, h_out, y, mean, rstd, rows, cols, eps,
                           (cudaStream_t)stream);
 }
@@ -292,6 +295,7 @@ LLMCTL_API int llmctl_layernorm_bwd(const void* dy, const void* h, const void* w
                                     const float* rstd, const void* dres, void* dx, float* dw,
                                     float* db, float* scratch, int scratch_rows, int rows, int cols,
                                     int accumulate, void* stream) {
+  LLMCTL_BEGIN();
   return launch_bwd<true>(dy, h, w, mean, rstd, dres, dx, dw, db, scratch, scratch_rows, rows, cols,
                           accumulate, (cudaStream_t)stream);
 }

@@ -117,6 +117,7 @@ LLMCTL_API int llmctl_adamw_step(void* master, void* m, void* v, const void* gra
                                  void* param_out, long long n, float lr, float beta1, float beta2,
                                  float eps, float weight_decay, float bias_corr1, float bias_corr2,
                                  float host_scale, const float* scale_dev, void* stream) {
+  LLMCTL_BEGIN();
   LLMCTL_REQUIRE(n >= 0);
   if (n == 0) return 0;
   long long blocks = ((n >> 3) + 255) / 256;
@@ -138,6 +139,7 @@ LLMCTL_API int llmctl_adamw_step(void* master, void* m, void* v, const void* gra
 // is min(scratch_elems, 8 * SMs).
 LLMCTL_API int llmctl_sumsq(const void* x, int is_fp32, long long n, float* scratch,
                             int scratch_elems, float* out, int accumulate, void* stream) {
+  LLMCTL_BEGIN();
   LLMCTL_REQUIRE(n >= 0 && scratch_elems >= 1);
   long long blocks = ((n >> 3) + 511) / 512;
   if (blocks < 1) blocks = 1;

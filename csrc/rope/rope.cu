@@ -53,6 +53,7 @@ using namespace llmctl;
 LLMCTL_API int llmctl_rope_inplace(void* x, long long row_stride, int n_tokens, int n_heads,
                                    int head_dim, const float* cos_t, const float* sin_t,
                                    const int* positions, int seq_len, float sign, void* stream) {
+  LLMCTL_BEGIN();
   LLMCTL_REQUIRE(head_dim % 16 == 0 && row_stride % 8 == 0 && seq_len > 0);
   const long long total = static_cast<long long>(n_tokens) * n_heads * (head_dim / 16);
   if (total == 0) return 0;

@@ -60,6 +60,7 @@ using namespace llmctl;
 
 LLMCTL_API int llmctl_swiglu_fwd(const void* gate_up, void* out, int M, int F, long long ld_gu,
                                  void* stream) {
+  LLMCTL_BEGIN();
   LLMCTL_REQUIRE(F % 8 == 0 && ld_gu % 8 == 0 && ld_gu >= 2LL * F);
   const long long total = static_cast<long long>(M) * (F / 8);
   if (total == 0) return 0;
@@ -72,6 +73,7 @@ LLMCTL_API int llmctl_swiglu_fwd(const void* gate_up, void* out, int M, int F, l
 
 LLMCTL_API int llmctl_swiglu_bwd(const void* dout, const void* gate_up, void* d_gate_up, int M,
                                  int F, long long ld_gu, void* stream) {
+  LLMCTL_BEGIN();
   LLMCTL_REQUIRE(F % 8 == 0 && ld_gu % 8 == 0 && ld_gu >= 2LL * F);
   const long long total = static_cast<long long>(M) * (F / 8);
   if (total == 0) return 0;

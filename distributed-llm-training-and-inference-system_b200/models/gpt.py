@@ -54,7 +54,7 @@ class Attention(nn.Module):
         d = cfg.heads * cfg.head_dim
         # packed projection; local rows are [q_local | k_local | v_local]
         self.qkv = tpl.ColumnParallelLinear(cfg.hidden, 3 * d, std=cfg.init_std, dtype=dtype, device=device,
-                                            fused_name="qkv")
+                                            fused_name="qkv", packed=3)
         self.out = tpl.RowParallelLinear(d, cfg.hidden, std=cfg.init_std / (2 * cfg.layers) ** 0.5, dtype=dtype,
                                          device=device, fused_name="attn_out")
 
@@ -76,7 +76,7 @@ class MLP(nn.Module):
         self.f_local = cfg.ffn // st.tp
         up_out = 2 * cfg.ffn if self.gated else cfg.ffn
         self.up = tpl.ColumnParallelLinear(cfg.hidden, up_out, std=cfg.init_std, dtype=dtype, device=device,
-                                           fused_name="mlp_up")
+                                           fused_name="mlp_up", packed=2 if self.gated else 1)
         self.down = tpl.RowParallelLinear(cfg.ffn, cfg.hidden, std=cfg.init_std / (2 * cfg.layers) ** 0.5,
                                           dtype=dtype, device=device, fused_name="mlp_down")
 

@@ -232,18 +232,19 @@ class _RopeFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, cos, sin, n_rot_heads, head_dim, seq_len, positions):
         assert x.dim() == 2 and x.stride(1) == 1
-        out = x.clone() if x.requires_grad or True else x
-        native.call("llmctl_rope_inplace", out.data_ptr(), out.stride(0), out.shape[0], n_rot_heads, head_dim,
+        # in place: the producer (the qkv GEMM) does not keep its output for backward
+        native.call("llmctl_rope_inplace", x.data_ptr(), x.stride(0), x.shape[0], n_rot_heads, head_dim,
                     cos.data_ptr(), sin.data_ptr(), native.ptr(positions), seq_len, 1.0, native.stream_ptr())
+        ctx.mark_dirty(x)
         ctx.save_for_backward(cos, sin, positions if positions is not None else torch.empty(0))
         ctx.meta = (n_rot_heads, head_dim, seq_len, positions is not None)
-        return out
+        return x
 
     @staticmethod
     def backward(ctx, dout):
         cos, sin, positions = ctx.saved_tensors
         n_rot, hd, seq_len, has_pos = ctx.meta
-        dx = dout.contiguous().clone()
+        dx = dout.clone(memory_format=torch.contiguous_format)   # never rotate a possibly shared grad in place
         native.call("llmctl_rope_inplace", dx.data_ptr(), dx.stride(0), dx.shape[0], n_rot, hd,
                     cos.data_ptr(), sin.data_ptr(), positions.data_ptr() if has_pos else None, seq_len, -1.0,
                     native.stream_ptr())
@@ -255,6 +256,8 @@ def rope_packed(x: torch.Tensor, cos, sin, n_rot_heads: int, head_dim: int, seq_
     """Apply RoPE to the first ``n_rot_heads`` heads of each row of ``x`` ``[tokens, H_total*head_dim]``
     (q heads then k heads in a packed q|k|v activation); the remaining columns pass through."""
     if _use_native(x, "elementwise"):
+        if x.is_leaf:
+            x = x.clone()   # never rotate a user-owned leaf in place
         return _RopeFn.apply(x, cos, sin, n_rot_heads, head_dim, seq_len,
                              None if positions is None else positions.to(torch.int32))
     T = x.shape[0]
@@ -394,17 +397,18 @@ class _CrossEntropyFn(torch.autograd.Function):
         rows, V = logits.shape
         loss_rows = torch.empty(rows, dtype=torch.float32, device=logits.device)
         need_grad = logits.requires_grad
+        # The kernel writes through the raw pointer; autograd is deliberately not told (mark_dirty cannot be
+        # combined with view inputs).  Safe because the producing GEMM does not keep its output for backward
+        # and the documented contract is that the caller never touches `logits` again.
         native.call("llmctl_cross_entropy_fwd_bwd", logits.data_ptr(), logits.stride(0), targets.data_ptr(),
                     loss_rows.data_ptr(), None, rows, V, ignore_index, float(grad_scale), inv_count.data_ptr(),
                     int(need_grad), native.stream_ptr())
-        ctx.save_for_backward(logits)
-        ctx.mark_dirty(logits)
+        ctx.save_for_backward(logits.detach())
         ctx.assume_unit = assume_unit_grad
-        loss = (loss_rows.sum() * inv_count).squeeze() * grad_scale
-        return loss, logits
+        return (loss_rows.sum() * inv_count).squeeze() * grad_scale
 
     @staticmethod
-    def backward(ctx, dloss, _dlogits):
+    def backward(ctx, dloss):
         (grad,) = ctx.saved_tensors
         if not ctx.assume_unit:
             grad = grad.mul_(dloss.to(grad.dtype))
@@ -426,8 +430,7 @@ def cross_entropy(logits: torch.Tensor, targets: torch.Tensor, ignore_index: int
             logits2 = logits2.clone()
         elif logits2.is_leaf:
             raise RuntimeError("cross_entropy(native) overwrites its input; pass a non-leaf tensor")
-        loss, _ = _CrossEntropyFn.apply(logits2, t.contiguous(), ignore_index, inv, grad_scale, assume_unit_grad)
-        return loss
+        return _CrossEntropyFn.apply(logits2, t.contiguous(), ignore_index, inv, grad_scale, assume_unit_grad)
     loss = F.cross_entropy(logits2.float(), t, ignore_index=ignore_index)
     return loss * grad_scale if grad_scale != 1.0 else loss
 

@@ -107,11 +107,15 @@ class NativeError(RuntimeError):
     pass
 
 
+#: kernels launched per entry point when it is not exactly one
+_KERNELS_PER_CALL = {"llmctl_rmsnorm_bwd": 2, "llmctl_layernorm_bwd": 3, "llmctl_sumsq": 2}
+
+
 def call(name: str, *args) -> None:
     """Invoke a C entry point and raise on a non-zero status."""
     global launch_count
     fn = getattr(lib(), name)
     rc = fn(*args)
-    launch_count += 1
+    launch_count += _KERNELS_PER_CALL.get(name, 1)
     if rc != 0:
         raise NativeError(f"{name} failed with cudaError {rc}")

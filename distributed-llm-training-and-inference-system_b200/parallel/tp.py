@@ -143,14 +143,15 @@ class ColumnParallelLinear(nn.Module):
     sequence parallelism — sharded on tokens and all-gathered first."""
 
     def __init__(self, in_features: int, out_features: int, *, std: float = 0.02, dtype=torch.bfloat16,
-                 device=None, fused_name: str = ""):
+                 device=None, fused_name: str = "", packed: int = 1):
         super().__init__()
         st = get_state()
-        assert out_features % st.tp == 0, f"{out_features} not divisible by tp={st.tp}"
+        assert out_features % (st.tp * packed) == 0, f"{out_features} not divisible by tp={st.tp} x packed={packed}"
         self.in_features, self.out_features = in_features, out_features
         self.out_local = out_features // st.tp
         self.weight = nn.Parameter(_init_weight((self.out_local, in_features), std, dtype, device))
         self.weight.tp_shard_dim = 0
+        self.weight.tp_packed = packed      # rows are `packed` equal groups (q|k|v, gate|up), each sharded
         self.fused_name = fused_name
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:

@@ -64,6 +64,9 @@ class ParamUnit:
                 self.replicated_numel = off
         self.dp = st.dp
         self.numel = _round_up(off, _ALIGN * self.dp)
+        # alignment gaps (between parameters and at the tail) must read as zero in gradient buckets
+        self.gaps = [(o + shp.numel(), nxt) for o, shp, nxt in
+                     zip(self.offsets, self.shapes, self.offsets[1:] + [self.numel]) if nxt > o + shp.numel()]
         self.shard_numel = self.numel // self.dp
         self.shard_lo = st.dp_rank * self.shard_numel
         self.shard_hi = self.shard_lo + self.shard_numel
@@ -128,7 +131,8 @@ class ParamUnit:
     def ensure_grad_bucket(self) -> None:
         if self.flat_grad is None:
             self.flat_grad = torch.empty(self.numel, dtype=self.grad_dtype, device=self.device)
-            self._bucket_fresh = True
+            for lo, hi in self.gaps:
+                self.flat_grad[lo:hi].zero_()
             self._pending = len(self.params)
             for p, o, shp in zip(self.params, self.offsets, self.shapes):
                 p.main_grad = self.flat_grad[o:o + shp.numel()].view(shp)
@@ -370,6 +374,16 @@ class ZeroOptimizer:
             u.exp_avg.copy_(s["exp_avg"])
             u.exp_avg_sq.copy_(s["exp_avg_sq"])
             self._publish(u)
+
+    def reset_from_params(self, step: int = 0) -> None:
+        """Rebuild fp32 master weights from the current parameters and zero the moments (used when a
+        checkpoint is resumed under a different plan, so the saved shards no longer line up)."""
+        self.step_count = step
+        with _FullParams(self):
+            for u in self.units:
+                u.master.copy_(u.flat_param[u.state_lo:u.state_hi])
+                u.exp_avg.zero_()
+                u.exp_avg_sq.zero_()
 
     def _publish(self, u: ParamUnit) -> None:
         """Write master weights back into the bf16 parameters (after a load)."""

@@ -61,7 +61,7 @@ class _HFWrapper:
 
 
 def load_tokenizer(path_or_name: Optional[str], vocab_size: int = 32000):
-    if path_or_name:
+    if isinstance(path_or_name, (str, Path)) and len(str(path_or_name)) < 1024:
         p = Path(str(path_or_name))
         if p.is_dir() and any((p / f).exists() for f in ("tokenizer.json", "tokenizer.model", "vocab.json")):
             try:

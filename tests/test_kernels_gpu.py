@@ -1,0 +1,199 @@
+"""Numerics of every hand-written sm_100a kernel against a plain PyTorch fp32 reference of the same op."""
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _close(a, b, atol, rtol, what=""):
+    a, b = a.float(), b.float()
+    err = (a - b).abs()
+    tol = atol + rtol * b.abs()
+    bad = (err > tol)
+    assert not bad.any(), (f"{what}: {int(bad.sum())}/{bad.numel()} mismatches, max err {err.max().item():.4g}, "
+                           f"first at {torch.nonzero(bad)[0].tolist()}")
+
+
+@pytest.mark.parametrize("rows,cols", [(64, 768), (4096, 4096), (1000, 5120), (33, 2048)])
+@pytest.mark.parametrize("with_res", [False, True])
+def test_rmsnorm_fwd_bwd(cuda_device, rows, cols, with_res):
+    from llmctl_b200.ops import functional as ops
+    torch.manual_seed(0)
+    x = torch.randn(rows, cols, device=cuda_device, dtype=torch.bfloat16, requires_grad=True)
+    r = torch.randn(rows, cols, device=cuda_device, dtype=torch.bfloat16, requires_grad=True) if with_res else None
+    w = (1 + 0.1 * torch.randn(cols, device=cuda_device)).to(torch.bfloat16).requires_grad_(True)
+    y, h = ops.rmsnorm(x, w, 1e-5, r)
+    dy = torch.randn_like(y)
+    dh = torch.randn_like(y)
+    (y.float() * dy.float()).sum().add((h.float() * dh.float()).sum()).backward()
+    # fp32 reference (same rounding point for h as the kernel: bf16)
+    xf = x.detach().float().requires_grad_(True)
+    rf = r.detach().float().requires_grad_(True) if with_res else None
+    wf = w.detach().float().requires_grad_(True)
+    hf = xf if rf is None else (xf + rf)
+    hq = hf + (hf.detach().to(torch.bfloat16).float() - hf.detach())   # straight-through bf16 rounding
+    yf = hq * torch.rsqrt(hq.pow(2).mean(-1, keepdim=True) + 1e-5) * wf
+    ((yf * dy.float()).sum() + (hq * dh.float()).sum()).backward()
+    _close(y, yf, 2e-2, 2e-2, "y")
+    _close(x.grad, xf.grad, 3e-2, 3e-2, "dx")
+    if with_res:
+        _close(r.grad, rf.grad, 3e-2, 3e-2, "dres")
+    _close(w.grad, wf.grad, 0.15 * math.sqrt(rows / 64), 3e-2, "dw")
+
+
+@pytest.mark.parametrize("rows,cols", [(256, 768), (2048, 4096)])
+def test_layernorm_fwd_bwd(cuda_device, rows, cols):
+    from llmctl_b200.ops import functional as ops
+    torch.manual_seed(1)
+    x = torch.randn(rows, cols, device=cuda_device, dtype=torch.bfloat16, requires_grad=True)
+    w = (1 + 0.1 * torch.randn(cols, device=cuda_device)).to(torch.bfloat16).requires_grad_(True)
+    b = (0.1 * torch.randn(cols, device=cuda_device)).to(torch.bfloat16).requires_grad_(True)
+    y, _ = ops.layernorm(x, w, b, 1e-5)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    xf, wf, bf = (t.detach().float().requires_grad_(True) for t in (x, w, b))
+    yf = F.layer_norm(xf, (cols,), wf, bf, 1e-5)
+    yf.backward(dy.float())
+    _close(y, yf, 2e-2, 2e-2, "y")
+    _close(x.grad, xf.grad, 3e-2, 3e-2, "dx")
+    _close(w.grad, wf.grad, 0.15 * math.sqrt(rows / 64), 3e-2, "dw")
+    _close(b.grad, bf.grad, 0.15 * math.sqrt(rows / 64), 3e-2, "db")
+
+
+def test_rope_fwd_bwd(cuda_device):
+    from llmctl_b200.ops import functional as ops
+    torch.manual_seed(2)
+    B, S, H, D = 2, 256, 8, 128
+    cos, sin = ops.rope_tables(D, S, device=cuda_device)
+    x = torch.randn(B * S, 3 * H * D, device=cuda_device, dtype=torch.bfloat16, requires_grad=True)
+    y = ops.rope_packed(x, cos, sin, 2 * H, D, S)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    xf = x.detach().float().requires_grad_(True)
+    rot = ops._rope_torch(xf[:, :2 * H * D].reshape(B * S, 2 * H, D), cos, sin, None, S, 1.0).reshape(B * S, -1)
+    yf = torch.cat([rot, xf[:, 2 * H * D:]], 1)
+    yf.backward(dy.float())
+    _close(y, yf, 2e-2, 2e-2, "y")
+    _close(x.grad, xf.grad, 2e-2, 2e-2, "dx")
+
+
+@pytest.mark.parametrize("M,Fd", [(512, 1376), (4096, 11008)])
+def test_swiglu_fwd_bwd(cuda_device, M, Fd):
+    from llmctl_b200.ops import functional as ops
+    torch.manual_seed(3)
+    gu = torch.randn(M, 2 * Fd, device=cuda_device, dtype=torch.bfloat16, requires_grad=True)
+    y = ops.swiglu(gu)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    gf = gu.detach().float().requires_grad_(True)
+    g, u = gf.chunk(2, -1)
+    yf = F.silu(g) * u
+    yf.backward(dy.float())
+    _close(y, yf, 2e-2, 2e-2, "y")
+    _close(gu.grad, gf.grad, 3e-2, 3e-2, "dgu")
+
+
+@pytest.mark.parametrize("grad_dtype", [torch.bfloat16, torch.float32])
+def test_adamw_matches_torch(cuda_device, grad_dtype):
+    from llmctl_b200.ops import optim
+    torch.manual_seed(4)
+    n = 1_000_003
+    p0 = torch.randn(n, device=cuda_device)
+    master, m, v = p0.clone(), torch.zeros_like(p0), torch.zeros_like(p0)
+    out = torch.empty(n, device=cuda_device, dtype=torch.bfloat16)
+    ref = torch.nn.Parameter(p0.clone())
+    opt = torch.optim.AdamW([ref], lr=1e-3, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1)
+    scale = torch.tensor([0.5], device=cuda_device)
+    for step in range(1, 4):
+        g = torch.randn(n, device=cuda_device).to(grad_dtype)
+        optim.adamw_step(master, m, v, g, out, step=step, lr=1e-3, beta1=0.9, beta2=0.95, eps=1e-8,
+                         weight_decay=0.1, grad_scale=2.0, scale_dev=scale)
+        ref.grad = g.float().clone()       # 2.0 * 0.5 = 1
+        opt.step()
+    _close(master, ref.detach(), 1e-5, 1e-5, "master")
+    _close(out, ref.detach(), 1e-2, 1e-2, "bf16 params")
+    # non-finite scale => step skipped
+    before = master.clone()
+    optim.adamw_step(master, m, v, g, out, step=4, lr=1e-3, beta1=0.9, beta2=0.95, eps=1e-8, weight_decay=0.1,
+                     scale_dev=torch.tensor([float("nan")], device=cuda_device))
+    assert torch.equal(before, master)
+
+
+def test_sumsq(cuda_device):
+    from llmctl_b200.ops import optim
+    x = torch.randn(3_000_017, device=cuda_device).to(torch.bfloat16)
+    out = torch.zeros(1, device=cuda_device)
+    optim.sumsq(x, out)
+    optim.sumsq(x, out, accumulate=True)
+    ref = 2 * x.float().pow(2).sum()
+    assert abs(out.item() - ref.item()) / ref.item() < 1e-4
+
+
+@pytest.mark.parametrize("rows,V", [(128, 32000), (1024, 32768), (64, 4096), (32, 50304)])
+def test_cross_entropy(cuda_device, rows, V):
+    from llmctl_b200.ops import functional as ops
+    torch.manual_seed(5)
+    base = (2 * torch.randn(rows, V, device=cuda_device)).to(torch.bfloat16)
+    t = torch.randint(0, V, (rows,), device=cuda_device)
+    t[::7] = -100
+    lin = base.clone().requires_grad_(True)
+    logits = lin * 1.0                    # non-leaf, consumed in place
+    loss = ops.cross_entropy(logits, t, grad_scale=0.5, assume_unit_grad=True)
+    loss.backward()
+    lf = base.float().requires_grad_(True)
+    lref = 0.5 * F.cross_entropy(lf, t, ignore_index=-100)
+    lref.backward()
+    assert abs(loss.item() - lref.item()) < 2e-3 * max(1.0, abs(lref.item()))
+    _close(lin.grad, lf.grad, 2e-5, 3e-2, "dlogits")
+
+
+GEMM_SHAPES = [(128, 256, 64), (256, 512, 256), (4096, 4096, 4096), (1000, 2752, 1376), (384, 136, 200),
+               (8192, 1024, 512)]
+
+
+@pytest.mark.parametrize("M,N,K", GEMM_SHAPES)
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, False), (True, True)])
+def test_gemm_layouts(cuda_device, M, N, K, a_mn, b_mn):
+    from llmctl_b200.ops import functional as ops
+    if (M % 8 and a_mn) or (N % 8):
+        pytest.skip("leading dims must be multiples of 8")
+    torch.manual_seed(6)
+    A = torch.randn(M, K, device=cuda_device).to(torch.bfloat16)
+    B = torch.randn(N, K, device=cuda_device).to(torch.bfloat16)
+    ref = A.float() @ B.float().t()
+    a_arg = A.t().contiguous() if a_mn else A
+    b_arg = B.t().contiguous() if b_mn else B
+    for tile_n in (128, 256):
+        out = ops.gemm_raw(a_arg, b_arg, a_mn=a_mn, b_mn=b_mn, tile_n=tile_n)
+        _close(out, ref, 0.05 * math.sqrt(K / 64), 2e-2, f"gemm tile_n={tile_n}")
+
+
+def test_gemm_fp32_accumulate(cuda_device):
+    from llmctl_b200.ops import functional as ops
+    torch.manual_seed(7)
+    M, N, K = 512, 768, 1024
+    A = torch.randn(M, K, device=cuda_device).to(torch.bfloat16)
+    B = torch.randn(N, K, device=cuda_device).to(torch.bfloat16)
+    C = torch.randn(M, N, device=cuda_device)
+    ref = C + A.float() @ B.float().t()
+    ops.gemm_raw(A, B, out=C, accumulate=True)
+    _close(C, ref, 1e-2, 1e-3, "fp32 accumulate")
+
+
+def test_linear_autograd(cuda_device):
+    from llmctl_b200.ops import functional as ops
+    torch.manual_seed(8)
+    x = torch.randn(4, 128, 1024, device=cuda_device).to(torch.bfloat16).requires_grad_(True)
+    w = (0.05 * torch.randn(2048, 1024, device=cuda_device)).to(torch.bfloat16).requires_grad_(True)
+    y = ops.linear(x, w)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    xf, wf = x.detach().float().requires_grad_(True), w.detach().float().requires_grad_(True)
+    yf = F.linear(xf, wf)
+    yf.backward(dy.float())
+    _close(y, yf, 5e-2, 2e-2, "y")
+    _close(x.grad, xf.grad, 5e-2, 2e-2, "dx")
+    _close(w.grad, wf.grad, 0.5, 2e-2, "dw")
