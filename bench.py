@@ -178,7 +178,7 @@ def run_native(args) -> dict:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms_per_step = float(ms.item()) / K
     value = tokens_per_step / (ms_per_step / 1e3)
-    final_loss = float(loss)
+    final_loss = float(loss.detach())
 
     # ---------------- end to end through the public API: H2D every step + D2H loss read -----------------
     e2e = None

@@ -1,5 +1,7 @@
 #include "tma_host.h"
 
+#include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <mutex>
@@ -57,12 +59,21 @@ static int encode_cached(CUtensorMap* out, const Key& key, int rank, const void*
   }
   EncodeTiledFn fn = resolve_encode();
   if (!fn) return static_cast<int>(cudaErrorNotSupported);
+  // Driver entry points need a current context on *this* thread (autograd worker threads may not have
+  // touched the runtime yet): a no-op runtime call binds the primary context.
+  (void)cudaFree(nullptr);
   cuuint32_t estr[3] = {1, 1, 1};
   CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(base), dims,
                   strides_bytes, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                   swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) return static_cast<int>(cudaErrorInvalidValue);
+  if (r != CUDA_SUCCESS) {
+    if (getenv("LLMCTL_DEBUG"))
+      fprintf(stderr, "[llmctl] cuTensorMapEncodeTiled failed: CUresult %d rank %d base %p dims %llu %llu box %u %u stride0 %llu\n",
+              (int)r, rank, base, (unsigned long long)dims[0], (unsigned long long)dims[1], box[0], box[1],
+              (unsigned long long)strides_bytes[0]);
+    return static_cast<int>(cudaErrorInvalidValue);
+  }
   std::lock_guard<std::mutex> lk(g_mu);
   if (g_cache.size() > 4096) g_cache.clear();
   g_cache.emplace(key, *out);

@@ -5,6 +5,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #define LLMCTL_API extern "C" __attribute__((visibility("default")))
 
@@ -13,22 +14,37 @@
 #define LLMCTL_BEGIN() (void)cudaGetLastError()
 
 // Every entry point returns a cudaError_t cast to int (0 == success).
-#define LLMCTL_RETURN_LAST()               \
-  do {                                     \
-    cudaError_t e__ = cudaGetLastError();  \
-    return static_cast<int>(e__);          \
+// Failures are described on stderr when LLMCTL_DEBUG is set in the environment.
+static inline bool llmctl_debug() {
+  static int v = -1;
+  if (v < 0) v = getenv("LLMCTL_DEBUG") ? 1 : 0;
+  return v == 1;
+}
+#define LLMCTL_FAIL(code, what)                                                          \
+  do {                                                                                   \
+    if (llmctl_debug())                                                                  \
+      fprintf(stderr, "[llmctl] %s:%d: %s (%d: %s)\n", __FILE__, __LINE__, what, (int)(code), \
+              cudaGetErrorString((cudaError_t)(code)));                                  \
+    return static_cast<int>(code);                                                       \
+  } while (0)
+
+#define LLMCTL_RETURN_LAST()                              \
+  do {                                                    \
+    cudaError_t e__ = cudaGetLastError();                 \
+    if (e__ != cudaSuccess) LLMCTL_FAIL(e__, "launch");   \
+    return 0;                                             \
   } while (0)
 
 #define LLMCTL_CHECK(expr)                               \
   do {                                                   \
     cudaError_t e__ = (expr);                            \
-    if (e__ != cudaSuccess) return static_cast<int>(e__);\
+    if (e__ != cudaSuccess) LLMCTL_FAIL(e__, #expr);     \
   } while (0)
 
 // Argument errors are reported as cudaErrorInvalidValue (1) so python raises uniformly.
-#define LLMCTL_REQUIRE(cond)                     \
-  do {                                           \
-    if (!(cond)) return static_cast<int>(cudaErrorInvalidValue); \
+#define LLMCTL_REQUIRE(cond)                                          \
+  do {                                                                \
+    if (!(cond)) LLMCTL_FAIL(cudaErrorInvalidValue, "require " #cond); \
   } while (0)
 
 namespace llmctl {

@@ -227,6 +227,221 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   }
 }
 
+
+// ================================================================================================
+// 2-CTA variant (cta_group::2): a CTA pair (cluster of 2, same TPC) computes one 256 x 256 tile.
+// CTA r stages A rows [m0 + 128 r, +128) and B rows (N) [n0 + 128 r, +128); the leader CTA issues
+// UMMA 256 x 256 x 16 which reads both CTAs' shared memory, so each SM moves only half of B through
+// its own shared memory (smem traffic per SM: 64 KB/stage-pair instead of 96 KB) — this is what lets
+// the tensor pipe stay fed.  Each CTA's TMEM holds its own 128 accumulator rows.
+//   full[s]   (leader only): 1 arrive (leader producer expect_tx of BOTH CTAs' bytes) + tx bytes
+//   empty[s]  (both CTAs)  : tcgen05.commit multicast from the leader
+//   tfull[a]  (both CTAs)  : tcgen05.commit multicast from the leader
+//   tempty[a] (leader only): 8 arrives = 4 epilogue warps x 2 CTAs (peer arrives remotely)
+// ================================================================================================
+struct Gemm2Cfg {
+  static constexpr int kBN = 256;            // N of the pair tile
+  static constexpr int kStages = 6;
+  static constexpr int kABytes = kBM * kBK * 2;          // 128 x 64 per CTA
+  static constexpr int kBBytes = (kBN / 2) * kBK * 2;    // 128 x 64 per CTA
+  static constexpr int kStageBytes = kABytes + kBBytes;  // 32 KB per CTA
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024;
+  static constexpr int kTmemCols = 512;
+};
+
+template <bool A_MN, bool B_MN, typename OutT>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
+gemm2_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                     OutT* __restrict__ C, long long ldc, int M, int N, int K, int beta) {
+  using Cfg = Gemm2Cfg;
+  constexpr int BN = Cfg::kBN;
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint64_t bar_full[Cfg::kStages];
+  __shared__ uint64_t bar_empty[Cfg::kStages];
+  __shared__ uint64_t bar_tfull[2];
+  __shared__ uint64_t bar_tempty[2];
+  __shared__ uint32_t tmem_base_smem;
+
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem = smem_raw + (smem_base - smem_u32(smem_raw));
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t cta_rank = cluster_ctarank();   // 0 = leader
+  const int pair = blockIdx.x >> 1;
+  const int num_pairs = gridDim.x >> 1;
+
+  const int num_m = (M + 2 * kBM - 1) / (2 * kBM);
+  const int num_n = (N + BN - 1) / BN;
+  const int num_tiles = num_m * num_n;
+  const int num_kb = (K + kBK - 1) / kBK;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < Cfg::kStages; ++i) {
+      mbar_init(&bar_full[i], 1);
+      mbar_init(&bar_empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&bar_tfull[i], 1);
+      mbar_init(&bar_tempty[i], 8);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmA);
+    prefetch_tmap(&tmB);
+  }
+  cluster_sync();   // barrier inits visible to the peer before any remote arrive / multicast commit
+  if (warp == 1) tmem_alloc<2>(&tmem_base_smem, Cfg::kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_smem;
+
+  if (warp == 0) {
+    // ------------------------------ TMA producer (both CTAs) ------------------------------
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = pair; tile < num_tiles; tile += num_pairs) {
+        const int m0 = (tile % num_m) * (2 * kBM) + static_cast<int>(cta_rank) * kBM;
+        const int n0 = (tile / num_m) * BN + static_cast<int>(cta_rank) * (BN / 2);
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&bar_empty[stage], phase ^ 1u);
+          uint8_t* sA = smem + stage * Cfg::kStageBytes;
+          uint8_t* sB = sA + Cfg::kABytes;
+          // all bytes of the pair are accounted on the leader's barrier
+          const uint32_t full_leader = mapa_u32(smem_u32(&bar_full[stage]), 0);
+          if (cta_rank == 0) mbar_expect_tx(&bar_full[stage], 2 * Cfg::kStageBytes);
+          const int k0 = kb * kBK;
+          if (!A_MN) {
+            tma_load_2d_cg2(sA, &tmA, full_leader, k0, m0);
+          } else {
+#pragma unroll
+            for (int g = 0; g < kBM / 64; ++g)
+              tma_load_2d_cg2(sA + g * 8192, &tmA, full_leader, m0 + g * 64, k0);
+          }
+          if (!B_MN) {
+            tma_load_2d_cg2(sB, &tmB, full_leader, k0, n0);
+          } else {
+#pragma unroll
+            for (int g = 0; g < (BN / 2) / 64; ++g)
+              tma_load_2d_cg2(sB + g * 8192, &tmB, full_leader, n0 + g * 64, k0);
+          }
+          if (++stage == Cfg::kStages) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------ MMA issuer (leader CTA only) ------------------------------
+    if (cta_rank == 0 && lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(2 * kBM, BN, A_MN ? 1u : 0u, B_MN ? 1u : 0u);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t aphase = 0;
+      for (int tile = pair; tile < num_tiles; tile += num_pairs) {
+        mbar_wait(&bar_tempty[acc], aphase ^ 1u);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * BN);
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&bar_full[stage], phase);
+          tc_fence_after();
+          const uint32_t a_addr = smem_base + stage * Cfg::kStageBytes;
+          const uint32_t b_addr = a_addr + Cfg::kABytes;
+#pragma unroll
+          for (int k = 0; k < kBK / 16; ++k) {
+            const uint64_t da = A_MN ? make_smem_desc(a_addr + k * 2048, 8192, 1024, 2)
+                                     : make_smem_desc(a_addr + k * 32, 16, 1024, 2);
+            const uint64_t db = B_MN ? make_smem_desc(b_addr + k * 2048, 8192, 1024, 2)
+                                     : make_smem_desc(b_addr + k * 32, 16, 1024, 2);
+            umma_ss<2>(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+          umma_commit_mc2(&bar_empty[stage], 0x3);   // both CTAs' slots are free once these retire
+          if (++stage == Cfg::kStages) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+        umma_commit_mc2(&bar_tfull[acc], 0x3);
+        acc ^= 1;
+        if (acc == 0) aphase ^= 1u;
+      }
+    }
+  } else {
+    // ------------------------------ epilogue (4 warps, both CTAs) ------------------------------
+    const int q = warp & 3;
+    int acc = 0;
+    uint32_t aphase = 0;
+    for (int tile = pair; tile < num_tiles; tile += num_pairs) {
+      const int m0 = (tile % num_m) * (2 * kBM) + static_cast<int>(cta_rank) * kBM;
+      const int n0 = (tile / num_m) * BN;
+      mbar_wait(&bar_tfull[acc], aphase);
+      tc_fence_after();
+      const int row = m0 + q * 32 + lane;
+      const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) +
+                             static_cast<uint32_t>(acc * BN);
+      OutT* crow = C + static_cast<long long>(row) * ldc + n0;
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_x32(t_row + c * 32, r);
+        tmem_ld_wait();
+        if (row < M) {
+          if constexpr (sizeof(OutT) == 2) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const int col = n0 + c * 32 + j * 8;
+              if (col < N) {
+                float f[8];
+#pragma unroll
+                for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(r[j * 8 + e]);
+                __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(crow) + c * 32 + j * 8;
+                if (beta) {
+                  float old[8];
+                  unpack8(load8(dst), old);
+#pragma unroll
+                  for (int e = 0; e < 8; ++e) f[e] += old[e];
+                }
+                store8(dst, pack8(f));
+              }
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const int col = n0 + c * 32 + j * 4;
+              if (col < N) {
+                float4 v = make_float4(__uint_as_float(r[j * 4]), __uint_as_float(r[j * 4 + 1]),
+                                       __uint_as_float(r[j * 4 + 2]), __uint_as_float(r[j * 4 + 3]));
+                float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(crow) + c * 32 + j * 4);
+                if (beta) {
+                  const float4 o = *dst;
+                  v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
+                }
+                *dst = v;
+              }
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(&bar_tempty[acc], 0);   // always the leader's barrier
+      acc ^= 1;
+      if (acc == 0) aphase ^= 1u;
+    }
+  }
+
+  tc_fence_before();
+  cluster_sync();   // the leader's MMAs read the peer's smem: nobody leaves before everything retired
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<2>(tmem_base, Cfg::kTmemCols);
+  }
+}
+
 static int g_num_sms = 0;
 static int num_sms() {
   if (g_num_sms == 0) {
@@ -248,10 +463,10 @@ static int launch_gemm(const void* A, const void* B, void* C, int M, int N, int 
   int rc;
   if (!A_MN) rc = get_tmap_2d_bf16(&tmA, A, M, K, lda, kBM, kBK, 1);
   else rc = get_tmap_2d_bf16(&tmA, A, K, M, lda, kBK, 64, 1);
-  if (rc) return rc;
+  if (rc) LLMCTL_FAIL(rc, "tensor map A");
   if (!B_MN) rc = get_tmap_2d_bf16(&tmB, B, N, K, ldb, BN, kBK, 1);
   else rc = get_tmap_2d_bf16(&tmB, B, K, N, ldb, kBK, 64, 1);
-  if (rc) return rc;
+  if (rc) LLMCTL_FAIL(rc, "tensor map B");
   auto kern = gemm_tcgen05_kernel<BN, A_MN, B_MN, OutT>;
   LLMCTL_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     Cfg::kSmemBytes));
@@ -273,12 +488,47 @@ static int dispatch_layout(int a_mn, int b_mn, const void* A, const void* B, voi
   return launch_gemm<BN, true, true, OutT>(A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s);
 }
 
+
+template <bool A_MN, bool B_MN, typename OutT>
+static int launch_gemm2(const void* A, const void* B, void* C, int M, int N, int K, long long lda,
+                        long long ldb, long long ldc, int beta, int max_ctas, cudaStream_t s) {
+  using Cfg = Gemm2Cfg;
+  CUtensorMap tmA, tmB;
+  int rc;
+  if (!A_MN) rc = get_tmap_2d_bf16(&tmA, A, M, K, lda, kBM, kBK, 1);
+  else rc = get_tmap_2d_bf16(&tmA, A, K, M, lda, kBK, 64, 1);
+  if (rc) LLMCTL_FAIL(rc, "tensor map A");
+  if (!B_MN) rc = get_tmap_2d_bf16(&tmB, B, N, K, ldb, Cfg::kBN / 2, kBK, 1);
+  else rc = get_tmap_2d_bf16(&tmB, B, K, N, ldb, kBK, 64, 1);
+  if (rc) LLMCTL_FAIL(rc, "tensor map B");
+  auto kern = gemm2_tcgen05_kernel<A_MN, B_MN, OutT>;
+  LLMCTL_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    Cfg::kSmemBytes));
+  const int tiles = ((M + 2 * kBM - 1) / (2 * kBM)) * ((N + Cfg::kBN - 1) / Cfg::kBN);
+  int pairs = num_sms() / 2;
+  if (max_ctas > 0 && max_ctas / 2 < pairs) pairs = max_ctas / 2;
+  if (pairs < 1) pairs = 1;
+  if (tiles < pairs) pairs = tiles;
+  kern<<<2 * pairs, kGemmThreads, Cfg::kSmemBytes, s>>>(tmA, tmB, (OutT*)C, ldc, M, N, K, beta);
+  LLMCTL_RETURN_LAST();
+}
+
+template <typename OutT>
+static int dispatch_layout2(int a_mn, int b_mn, const void* A, const void* B, void* C, int M, int N,
+                            int K, long long lda, long long ldb, long long ldc, int beta,
+                            int max_ctas, cudaStream_t s) {
+  if (!a_mn && !b_mn) return launch_gemm2<false, false, OutT>(A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s);
+  if (!a_mn && b_mn) return launch_gemm2<false, true, OutT>(A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s);
+  if (a_mn && !b_mn) return launch_gemm2<true, false, OutT>(A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s);
+  return launch_gemm2<true, true, OutT>(A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s);
+}
+
 }  // namespace llmctl
 
 using namespace llmctl;
 
 // D[M,N] = op(A) op(B) (+ D if beta).  a_mn / b_mn select the operand storage (see file header).
-// out_fp32: D is fp32 (else bf16).  tile_n: 0 = auto, 128 or 256.  max_ctas: 0 = all SMs
+// out_fp32: D is fp32 (else bf16).  tile_n: 0 = auto, 128 or 256 (1-CTA tiles), 2 = 256x256 CTA-pair tile.  max_ctas: 0 = all SMs
 // (a smaller value leaves SMs free for a concurrent communication kernel).
 LLMCTL_API int llmctl_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K,
                                 long long lda, long long ldb, long long ldc, int a_mn, int b_mn,
@@ -290,13 +540,20 @@ LLMCTL_API int llmctl_gemm_bf16(const void* A, const void* B, void* C, int M, in
                  (reinterpret_cast<uintptr_t>(C) & 15) == 0);
   LLMCTL_REQUIRE(out_fp32 ? (ldc % 4 == 0) : (ldc % 8 == 0));
   cudaStream_t s = (cudaStream_t)stream;
+  // auto: the CTA-pair kernel wins whenever the problem has at least one full pair tile in each dimension
+  // (measured on B200: 1.44-1.61 PFLOP/s vs 1.24-1.45 for the single-CTA 128x256 tile on the GPT-7B shapes)
+  if (tile_n == 0 && M > 128 && N > 128) tile_n = 2;
+  if (tile_n == 2) {   // 2-CTA pair tile 256 x 256 (cta_group::2)
+    if (out_fp32) return dispatch_layout2<float>(a_mn, b_mn, A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s);
+    return dispatch_layout2<__nv_bfloat16>(a_mn, b_mn, A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s);
+  }
   int bn = tile_n;
   if (bn != 128 && bn != 256) {
     const int sms = num_sms();
     const long long t256 = static_cast<long long>((M + 127) / 128) * ((N + 255) / 256);
     const long long t128 = static_cast<long long>((M + 127) / 128) * ((N + 127) / 128);
     const double c256 = static_cast<double>((t256 + sms - 1) / sms) * 2.0;
-    const double c128 = static_cast<double>((t128 + sms - 1) / sms) * 1.12;
+    const double c128 = static_cast<double>((t128 + sms - 1) / sms) * 1.45;  // measured: a 128-wide tile runs at ~0.7x the rate
     bn = (c128 < c256) ? 128 : 256;
   }
   if (bn == 256) {

@@ -23,6 +23,7 @@ import torch.nn.functional as F
 from ..comms.mesh import get_state
 from ..exec.checkpointing import checkpoint_layer
 from ..ops import functional as ops
+from ..ops.attention import rope_attention_packed
 from ..parallel import tp as tpl
 from .config import ModelConfig
 
@@ -62,10 +63,8 @@ class Attention(nn.Module):
                 positions: Optional[torch.Tensor] = None) -> torch.Tensor:
         H, D = self.heads_local, self.head_dim
         qkv = self.qkv(x)                                        # [T, 3*H*D]
-        qkv = ops.rope_packed(qkv, rope[0], rope[1], 2 * H, D, seq, positions)
-        v5 = qkv.view(batch, seq, 3, H, D)
-        o = ops.attention(v5[:, :, 0], v5[:, :, 1], v5[:, :, 2], causal=True)   # [B,S,H,D]
-        return self.out(o.reshape(batch * seq, H * D))
+        o = rope_attention_packed(qkv, rope[0], rope[1], batch, seq, H, D, positions)   # [T, H*D]
+        return self.out(o)
 
 
 class MLP(nn.Module):

@@ -95,3 +95,131 @@ def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, causal: bool = 
     if _native_ok(q, k, v):
         return _FlashAttnFn.apply(q, k, v, scale, causal)
     return _sdpa(q, k, v, causal, scale)
+
+
+# ------------------------------------------------------------------------------------------------------
+# Packed RoPE + attention: one autograd node over the packed [tokens, 3*H*D] activation.
+# Slicing q/k/v out of the packed tensor through autograd costs three zero-fills, three copies and two adds
+# of the full activation in backward; here the backward writes dq|dk|dv straight into one packed buffer and
+# applies the inverse rotation in place on it.
+# ------------------------------------------------------------------------------------------------------
+_sdpa_impl = {"name": None}
+
+
+def _sdpa_fwd_bwd_ops():
+    """Pick the library attention op pair once (cudnn flash on sm_100, else flash-attn 2)."""
+    if _sdpa_impl["name"] is None:
+        _sdpa_impl["name"] = "cudnn"
+    return _sdpa_impl["name"]
+
+
+def _lib_attention_fwd(q, k, v, scale, causal):
+    """q,k,v: [B,H,S,D] views.  Returns (out [B,H,S,D], saved-for-backward tuple)."""
+    impl = _sdpa_fwd_bwd_ops()
+    if impl == "cudnn":
+        try:
+            r = torch.ops.aten._scaled_dot_product_cudnn_attention(q, k, v, None, True, 0.0, causal, False, scale=scale)
+            return r[0], ("cudnn",) + tuple(r[1:8])
+        except Exception:  # noqa: BLE001
+            _sdpa_impl["name"] = impl = "flash"
+    if impl == "flash":
+        r = torch.ops.aten._scaled_dot_product_flash_attention(q, k, v, 0.0, causal, False, scale=scale)
+        return r[0], ("flash",) + tuple(r[1:8])
+    raise RuntimeError("no library attention op available")
+
+
+def _lib_attention_bwd(do, q, k, v, out, saved, scale, causal):
+    kind = saved[0]
+    lse, cq, ck, mq, mk, seed, off = saved[1:8]
+    if kind == "cudnn":
+        bias = torch.empty(0, device=q.device, dtype=q.dtype)
+        try:
+            return torch.ops.aten._scaled_dot_product_cudnn_attention_backward(
+                do, q, k, v, out, lse, seed, off, None, cq, ck, mq, mk, 0.0, causal, scale=scale)
+        except Exception:  # noqa: BLE001
+            return torch.ops.aten._scaled_dot_product_cudnn_attention_backward(
+                do, q, k, v, out, lse, seed, off, bias, cq, ck, mq, mk, 0.0, causal, scale=scale)
+    return torch.ops.aten._scaled_dot_product_flash_attention_backward(
+        do, q, k, v, out, lse, cq, ck, mq, mk, 0.0, causal, seed, off, scale=scale)
+
+
+class _RopeAttnPackedFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, qkv, cos, sin, B, S, H, D, positions, scale, use_native):
+        T = B * S
+        # RoPE in place on the q and k heads (the producing GEMM does not keep its output)
+        native.call("llmctl_rope_inplace", qkv.data_ptr(), qkv.stride(0), T, 2 * H, D, cos.data_ptr(), sin.data_ptr(),
+                    native.ptr(positions), S, 1.0, native.stream_ptr())
+        v5 = qkv.detach().view(B, S, 3, H, D)
+        q, k, v = v5[:, :, 0], v5[:, :, 1], v5[:, :, 2]
+        if use_native:
+            o = torch.empty(B, S, H, D, dtype=qkv.dtype, device=qkv.device)
+            lse = torch.empty(B, H, S, dtype=torch.float32, device=qkv.device)
+            native.call("llmctl_flash_attn_fwd", q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), lse.data_ptr(),
+                        B, S, H, D, q.stride(1), k.stride(1), v.stride(1), o.stride(1), float(scale), 1,
+                        native.stream_ptr())
+            ctx.lib_saved = None
+            ctx.save_for_backward(qkv.detach(), o, lse, cos, sin, positions if positions is not None else torch.empty(0))
+            out = o
+        else:
+            o_bhsd, saved = _lib_attention_fwd(q.transpose(1, 2), k.transpose(1, 2), v.transpose(1, 2), scale, True)
+            ctx.lib_saved = (saved[0],) + tuple(x for x in saved[1:])
+            ctx.save_for_backward(qkv.detach(), o_bhsd, saved[1], cos, sin,
+                                  positions if positions is not None else torch.empty(0))
+            out = o_bhsd.transpose(1, 2)
+        ctx.meta = (B, S, H, D, positions is not None, scale, use_native)
+        return out.reshape(T, H * D)
+
+    @staticmethod
+    def backward(ctx, do):
+        qkv, o, lse, cos, sin, positions = ctx.saved_tensors
+        B, S, H, D, has_pos, scale, use_native = ctx.meta
+        T = B * S
+        v5 = qkv.view(B, S, 3, H, D)
+        q, k, v = v5[:, :, 0], v5[:, :, 1], v5[:, :, 2]
+        dqkv = torch.empty(T, 3 * H * D, dtype=qkv.dtype, device=qkv.device)
+        d5 = dqkv.view(B, S, 3, H, D)
+        do4 = do.reshape(B, S, H, D)
+        if use_native and native.has_symbol("llmctl_flash_attn_bwd"):
+            do4 = do4.contiguous()
+            scratch = torch.empty(B * H * S * (D + 1), dtype=torch.float32, device=qkv.device)
+            native.call("llmctl_flash_attn_bwd", q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), do4.data_ptr(),
+                        lse.data_ptr(), d5[:, :, 0].data_ptr(), d5[:, :, 1].data_ptr(), d5[:, :, 2].data_ptr(),
+                        scratch.data_ptr(), B, S, H, D, q.stride(1), k.stride(1), v.stride(1), o.stride(1),
+                        d5.stride(1), float(scale), 1, native.stream_ptr())
+        else:
+            if use_native:
+                # native forward, library backward: recompute the library forward to get its saved state
+                o_b, saved = _lib_attention_fwd(q.transpose(1, 2), k.transpose(1, 2), v.transpose(1, 2), scale, True)
+            else:
+                o_b, saved = o, ctx.lib_saved
+            dq, dk, dv = _lib_attention_bwd(do4.transpose(1, 2), q.transpose(1, 2), k.transpose(1, 2),
+                                            v.transpose(1, 2), o_b, saved, scale, True)
+            d5[:, :, 0].copy_(dq.transpose(1, 2))
+            d5[:, :, 1].copy_(dk.transpose(1, 2))
+            d5[:, :, 2].copy_(dv.transpose(1, 2))
+        native.call("llmctl_rope_inplace", dqkv.data_ptr(), dqkv.stride(0), T, 2 * H, D, cos.data_ptr(), sin.data_ptr(),
+                    positions.data_ptr() if has_pos else None, S, -1.0, native.stream_ptr())
+        return dqkv, None, None, None, None, None, None, None, None, None
+
+
+def rope_attention_packed(qkv: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor, batch: int, seq: int,
+                          heads: int, head_dim: int, positions: Optional[torch.Tensor] = None,
+                          scale: Optional[float] = None) -> torch.Tensor:
+    """RoPE(q,k) + causal attention on a packed ``[batch*seq, 3*heads*head_dim]`` activation (rows are
+    ``q|k|v``).  Returns ``[batch*seq, heads*head_dim]``.  CUDA/bf16 with the native element-wise kernels
+    enabled uses the fused autograd node above; everything else composes the generic ops."""
+    from . import functional as ops
+    scale = scale if scale is not None else 1.0 / math.sqrt(head_dim)
+    cfg = kernel_config()
+    if (qkv.is_cuda and qkv.dtype == torch.bfloat16 and cfg.elementwise == "native" and qkv.dim() == 2
+            and qkv.stride(1) == 1 and not qkv.is_leaf and head_dim % 16 == 0):
+        v5 = qkv.view(batch, seq, 3, heads, head_dim)
+        use_native = _native_ok(v5[:, :, 0], v5[:, :, 1], v5[:, :, 2]) and \
+            (native.has_symbol("llmctl_flash_attn_bwd") or not torch.is_grad_enabled())
+        pos = None if positions is None else positions.to(torch.int32)
+        return _RopeAttnPackedFn.apply(qkv, cos, sin, batch, seq, heads, head_dim, pos, scale, use_native)
+    qkv = ops.rope_packed(qkv, cos, sin, 2 * heads, head_dim, seq, positions)
+    v5 = qkv.view(batch, seq, 3, heads, head_dim)
+    o = attention(v5[:, :, 0], v5[:, :, 1], v5[:, :, 2], causal=True, scale=scale)
+    return o.reshape(batch * seq, heads * head_dim)

@@ -166,7 +166,7 @@ def test_gemm_layouts(cuda_device, M, N, K, a_mn, b_mn):
     ref = A.float() @ B.float().t()
     a_arg = A.t().contiguous() if a_mn else A
     b_arg = B.t().contiguous() if b_mn else B
-    for tile_n in (128, 256):
+    for tile_n in (128, 256, 2):
         out = ops.gemm_raw(a_arg, b_arg, a_mn=a_mn, b_mn=b_mn, tile_n=tile_n)
         _close(out, ref, 0.05 * math.sqrt(K / 64), 2e-2, f"gemm tile_n={tile_n}")
 
@@ -181,6 +181,10 @@ def test_gemm_fp32_accumulate(cuda_device):
     ref = C + A.float() @ B.float().t()
     ops.gemm_raw(A, B, out=C, accumulate=True)
     _close(C, ref, 1e-2, 1e-3, "fp32 accumulate")
+    C2 = torch.randn(M, N, device=cuda_device)
+    ref2 = C2 + A.float() @ B.float().t()
+    ops.gemm_raw(A, B, out=C2, accumulate=True, tile_n=2)
+    _close(C2, ref2, 1e-2, 1e-3, "fp32 accumulate (2-CTA)")
 
 
 def test_linear_autograd(cuda_device):

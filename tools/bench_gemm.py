@@ -13,7 +13,8 @@ SHAPES = [  # (M, N, K, a_mn, b_mn, name)
     (4096, 32000, 4096, 0, 0, "lm_head fwd"),
     (4096, 4096, 12288, 0, 1, "qkv dgrad"), (4096, 11008, 4096, 0, 1, "down dgrad"),
     (12288, 4096, 4096, 1, 1, "qkv wgrad"), (22016, 4096, 4096, 1, 1, "gate_up wgrad"),
-    (4096, 11008, 4096, 1, 1, "down wgrad"), (8192, 8192, 8192, 0, 0, "8192^3"),
+    (4096, 11008, 4096, 1, 1, "down wgrad"), (4096, 4096, 22016, 0, 1, "gate_up dgrad"), (4096, 4096, 4096, 1, 1, "attn_out wgrad"),
+    (8192, 8192, 8192, 0, 0, "8192^3"),
 ]
 
 def time_fn(fn, flush, iters=10, warm=3):
@@ -29,7 +30,7 @@ def time_fn(fn, flush, iters=10, warm=3):
     return ts[len(ts) // 2], ts[0]
 
 def main():
-    ap = argparse.ArgumentParser(); ap.add_argument("--out", default=None); ap.add_argument("--tiles", default="0,128,256")
+    ap = argparse.ArgumentParser(); ap.add_argument("--out", default=None); ap.add_argument("--tiles", default="256,2")
     a = ap.parse_args()
     dev = torch.device("cuda")
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
