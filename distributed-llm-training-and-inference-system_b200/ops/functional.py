@@ -256,8 +256,8 @@ def rope_packed(x: torch.Tensor, cos, sin, n_rot_heads: int, head_dim: int, seq_
     """Apply RoPE to the first ``n_rot_heads`` heads of each row of ``x`` ``[tokens, H_total*head_dim]``
     (q heads then k heads in a packed q|k|v activation); the remaining columns pass through."""
     if _use_native(x, "elementwise"):
-        if x.is_leaf:
-            x = x.clone()   # never rotate a user-owned leaf in place
+        if x.is_leaf and x.requires_grad:
+            x = x.clone()   # never rotate a trainable leaf in place (other inputs ARE rotated in place)
         return _RopeFn.apply(x, cos, sin, n_rot_heads, head_dim, seq_len,
                              None if positions is None else positions.to(torch.int32))
     T = x.shape[0]

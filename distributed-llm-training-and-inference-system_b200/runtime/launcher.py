@@ -1,0 +1,208 @@
+"""Process launchers (local torchrun / Slurm / MPI) and the orchestrator that streams worker output.
+
+Surface of reference llmctl/runtime/launcher.py:21-332 (``LaunchConfig``, ``BaseLauncher``,
+``LocalLauncher``, ``SlurmLauncher``, ``MPILauncher``, ``create_launcher``, ``ProcessOrchestrator``).
+Fixed on purpose: ``sys.executable`` instead of ``python``, a free rendezvous port
+bound to 127.0.0.1 instead of a hard-coded 29500/localhost, no forced ``CUDA_VISIBLE_DEVICES``, elastic
+restarts (``--max-restarts``) with auto-resume, ``k8s`` fails with a clear message (E7), MPI ranks come
+from the real OMPI environment instead of a constant 0.
+"""
+from __future__ import annotations
+
+import os
+import signal
+import socket
+import subprocess
+import sys
+import tempfile
+from abc import ABC, abstractmethod
+from dataclasses import dataclass, field
+from pathlib import Path
+from typing import Dict, List, Optional
+
+
+@dataclass
+class LaunchConfig:
+    launcher: str = "local"
+    nodes: int = 1
+    gpus_per_node: int = 1
+    cpus_per_task: Optional[int] = None
+    backend: str = "nccl"
+    master_addr: str = "127.0.0.1"
+    master_port: Optional[int] = None
+    plan_path: Optional[str] = None
+    config_path: Optional[str] = None
+    data_path: Optional[str] = None
+    checkpoint_path: Optional[str] = None
+    output_dir: str = "./outputs"
+    mixed_precision: str = "bf16"
+    seed: int = 42
+    deterministic: bool = False
+    log_level: str = "info"
+    max_restarts: int = 0
+    nccl_debug: Optional[str] = None
+    env: Dict[str, str] = field(default_factory=dict)
+    slurm_partition: Optional[str] = None
+    slurm_time: str = "24:00:00"
+    slurm_account: Optional[str] = None
+
+
+def free_port() -> int:
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+class BaseLauncher(ABC):
+    def __init__(self, config: LaunchConfig):
+        self.config = config
+
+    @abstractmethod
+    def build_command(self, script: str, script_args: List[str]) -> List[str]:
+        ...
+
+    def environment(self) -> Dict[str, str]:
+        c = self.config
+        env = dict(os.environ)
+        env.update(c.env)
+        root = str(Path(__file__).resolve().parents[2])
+        env["PYTHONPATH"] = root + (os.pathsep + env["PYTHONPATH"] if env.get("PYTHONPATH") else "")
+        if c.nccl_debug:
+            env["NCCL_DEBUG"] = c.nccl_debug
+        if c.deterministic:
+            env["PYTHONHASHSEED"] = str(c.seed)
+            env["CUBLAS_WORKSPACE_CONFIG"] = ":4096:8"
+            env["NCCL_ALGO"] = env.get("NCCL_ALGO", "Ring")      # fixed reduction order
+        return env
+
+    @abstractmethod
+    def launch(self, script: str, script_args: List[str]) -> subprocess.Popen:
+        ...
+
+
+class LocalLauncher(BaseLauncher):
+    def build_command(self, script, script_args):
+        c = self.config
+        port = c.master_port or free_port()
+        cmd = [sys.executable, "-m", "torch.distributed.run", f"--nnodes={c.nodes}",
+               f"--nproc-per-node={c.gpus_per_node}", "--master-addr", c.master_addr, "--master-port", str(port)]
+        if c.max_restarts:
+            cmd += [f"--max-restarts={c.max_restarts}"]
+        return cmd + [script] + list(script_args)
+
+    def launch(self, script, script_args):
+        return subprocess.Popen(self.build_command(script, script_args), env=self.environment(),
+                                stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, bufsize=1,
+                                start_new_session=True)
+
+
+class SlurmLauncher(BaseLauncher):
+    def sbatch_script(self, script, script_args) -> str:
+        c = self.config
+        lines = ["#!/bin/bash", "#SBATCH --job-name=llmctl-train", f"#SBATCH --nodes={c.nodes}",
+                 "#SBATCH --ntasks-per-node=1", f"#SBATCH --gpus-per-node={c.gpus_per_node}",
+                 f"#SBATCH --time={c.slurm_time}", f"#SBATCH --output={c.output_dir}/slurm-%j.out"]
+        if c.cpus_per_task:
+            lines.append(f"#SBATCH --cpus-per-task={c.cpus_per_task}")
+        if c.slurm_partition:
+            lines.append(f"#SBATCH --partition={c.slurm_partition}")
+        if c.slurm_account:
+            lines.append(f"#SBATCH --account={c.slurm_account}")
+        root = str(Path(__file__).resolve().parents[2])
+        lines += ["", "export MASTER_ADDR=$(scontrol show hostnames $SLURM_JOB_NODELIST | head -n 1)",
+                  f"export MASTER_PORT={c.master_port or 29500}", f"export PYTHONPATH={root}:$PYTHONPATH"]
+        if c.nccl_debug:
+            lines.append(f"export NCCL_DEBUG={c.nccl_debug}")
+        args = " ".join(script_args)
+        lines += ["", f"srun {sys.executable} -m torch.distributed.run --nnodes=$SLURM_JOB_NUM_NODES "
+                      f"--nproc-per-node={c.gpus_per_node} --rdzv-backend=c10d --rdzv-endpoint=$MASTER_ADDR:$MASTER_PORT "
+                      f"--max-restarts={c.max_restarts} {script} {args}", ""]
+        return "\n".join(lines)
+
+    def build_command(self, script, script_args):
+        fd, path = tempfile.mkstemp(prefix="llmctl_", suffix=".sbatch")
+        with os.fdopen(fd, "w") as f:
+            f.write(self.sbatch_script(script, script_args))
+        self.script_path = path
+        return ["sbatch", path]
+
+    def launch(self, script, script_args):
+        return subprocess.Popen(self.build_command(script, script_args), env=self.environment(),
+                                stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+
+
+class MPILauncher(BaseLauncher):
+    def build_command(self, script, script_args):
+        c = self.config
+        n = c.nodes * c.gpus_per_node
+        port = c.master_port or free_port()
+        # the worker maps OMPI_COMM_WORLD_RANK / _LOCAL_RANK / _SIZE onto RANK / LOCAL_RANK / WORLD_SIZE
+        return ["mpirun", "-np", str(n), "--bind-to", "none", "--map-by", "slot", "-x", "PYTHONPATH",
+                "-x", f"MASTER_ADDR={c.master_addr}", "-x", f"MASTER_PORT={port}",
+                sys.executable, script] + list(script_args)
+
+    def launch(self, script, script_args):
+        return subprocess.Popen(self.build_command(script, script_args), env=self.environment(),
+                                stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+
+
+def create_launcher(config: LaunchConfig) -> BaseLauncher:
+    kind = config.launcher.lower()
+    if kind == "local":
+        return LocalLauncher(config)
+    if kind == "slurm":
+        return SlurmLauncher(config)
+    if kind == "mpi":
+        return MPILauncher(config)
+    if kind == "k8s":
+        raise ValueError("launcher 'k8s' is declared by the CLI but not available in this build (single-node "
+                         "NVSwitch target); use local, slurm or mpi")
+    raise ValueError(f"unknown launcher {config.launcher!r} (local | slurm | mpi | k8s)")
+
+
+class ProcessOrchestrator:
+    """Starts the launcher process, streams its output, forwards Ctrl-C as SIGTERM then SIGKILL after 5 s
+    (to the process *group* we started — never by name pattern)."""
+
+    def __init__(self, config: LaunchConfig):
+        self.config = config
+        self.launcher = create_launcher(config)
+        self.process: Optional[subprocess.Popen] = None
+
+    def start_training(self, script: str, script_args: List[str], echo=print) -> int:
+        self.process = self.launcher.launch(script, script_args)
+        if self.config.launcher != "local":
+            out, _ = self.process.communicate()
+            echo(out or "")
+            return self.process.returncode
+        try:
+            for line in self.process.stdout:
+                echo(line.rstrip("\n"))
+            return self.process.wait()
+        except KeyboardInterrupt:
+            self.stop_training()
+            return 130
+
+    def stop_training(self) -> None:
+        p = self.process
+        if p is None or p.poll() is not None:
+            return
+        try:
+            os.killpg(p.pid, signal.SIGTERM)
+        except (ProcessLookupError, PermissionError):
+            p.terminate()
+        try:
+            p.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            try:
+                os.killpg(p.pid, signal.SIGKILL)
+            except (ProcessLookupError, PermissionError):
+                p.kill()
+
+    def get_status(self) -> Dict[str, object]:
+        p = self.process
+        if p is None:
+            return {"status": "not_started"}
+        rc = p.poll()
+        return {"status": "running" if rc is None else ("completed" if rc == 0 else "failed"), "pid": p.pid,
+                "returncode": rc}

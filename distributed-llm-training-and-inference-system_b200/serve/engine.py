@@ -1,0 +1,310 @@
+"""Inference engine: paged KV cache, continuous batching, native decode kernels.
+
+One ``step()`` = one scheduler step: newly admitted sequences are prefilled (dense causal attention over the
+prompt, K/V scattered into their cache blocks — kernel K13), all running sequences then decode one token
+together (packed qkv GEMM, RoPE at each sequence's own position, K13 append, K12 paged attention over the
+block tables, K14 batched sampling) and finished sequences free their blocks.  Nothing in the step reads
+a value back to the host except the sampled token ids (one small D2H copy per step).
+
+Reference: reference llmctl/serve/server.py:127-251 ``InferenceEngine.generate_batch`` right-pads the batch,
+re-runs the HF model over the full sequences (``use_cache`` result discarded), samples from the pad position
+(D2) with a host sync per request and never re-queues unfinished requests (D1).
+"""
+from __future__ import annotations
+
+import json
+import math
+import threading
+import time
+from dataclasses import dataclass, field
+from pathlib import Path
+from typing import Dict, List, Optional, Tuple
+
+import torch
+import torch.nn.functional as F
+
+from ..comms.mesh import get_state
+from ..models.config import ModelConfig, resolve_model
+from ..models.gpt import GPTModel, build_model
+from ..ops import functional as ops
+from ..ops import serving as sops
+from .native_host import DECODE, PREFILL, BatchScheduler, KVBlockManager
+from .tokenizer import load_tokenizer
+
+
+def load_model_for_inference(artifact: str | Path, device: Optional[str] = None, dtype: Optional[torch.dtype] = None
+                             ) -> Tuple[GPTModel, ModelConfig, object, torch.device]:
+    """Load a checkpoint / exported artifact directory (``model_config.json`` + ``model.safetensors`` or TP/PP
+    shards), or build a random-init preset when ``artifact`` names one (benchmarks)."""
+    from ..io.export import consolidate_to_state_dict, shard_state_dict_for
+    st = get_state()
+    if device in (None, "auto"):
+        dev = st.device if st.world_size > 1 else torch.device("cuda" if torch.cuda.is_available() else "cpu")
+    else:
+        dev = torch.device(device)
+    dtype = dtype or (torch.bfloat16 if dev.type == "cuda" else torch.float32)
+    p = Path(str(artifact))
+    if p.is_dir():
+        mcfg = ModelConfig.from_file(p / "model_config.json")
+        model = build_model(mcfg, dtype=dtype, device=dev)
+        full = consolidate_to_state_dict(p)
+        if any(k.startswith("model.layers.") for k in full):
+            raise ValueError("artifact uses HF tensor names; re-export without --hf-names to serve it here")
+        local = shard_state_dict_for(full, model)
+        with torch.no_grad():
+            for k, prm in model.named_parameters():
+                prm.copy_(local[k].to(dev, dtype))
+    else:
+        mcfg = resolve_model(str(artifact))
+        model = build_model(mcfg, dtype=dtype, device=dev)
+    model.eval()
+    for prm in model.parameters():
+        prm.requires_grad_(False)
+    tok = load_tokenizer(str(artifact), mcfg.vocab_size)
+    return model, mcfg, tok, dev
+
+
+@dataclass
+class Sequence:
+    req_id: int
+    prompt_ids: List[int]
+    max_tokens: int
+    temperature: float = 1.0
+    top_p: float = 1.0
+    top_k: int = -1
+    generated: List[int] = field(default_factory=list)
+    finished: bool = False
+    finish_reason: Optional[str] = None
+    created: float = field(default_factory=time.time)
+    first_token_time: Optional[float] = None
+    on_token: Optional[object] = None      # callback(seq, token) for streaming
+    done_event: threading.Event = field(default_factory=threading.Event)
+
+    @property
+    def all_ids(self) -> List[int]:
+        return self.prompt_ids + self.generated
+
+
+class InferenceEngine:
+    def __init__(self, artifact: str | Path, *, max_batch_size: int = 8, max_batch_tokens: int = 8192,
+                 scheduler: str = "dynamic", device: Optional[str] = None, kv_block_size: int = 16,
+                 kv_memory_fraction: float = 0.5, num_kv_blocks: Optional[int] = None, seed: int = 0):
+        self.model, self.cfg, self.tokenizer, self.device = load_model_for_inference(artifact, device)
+        self.st = get_state()
+        m = self.model
+        self.heads_local = m.blocks[0].attn.heads_local
+        self.head_dim = self.cfg.head_dim
+        self.block_size = kv_block_size
+        self.dtype = next(m.parameters()).dtype
+        if num_kv_blocks is None:
+            per_block = 2 * len(m.blocks) * kv_block_size * self.heads_local * self.head_dim * self.dtype.itemsize
+            if self.device.type == "cuda":
+                free, _ = torch.cuda.mem_get_info(self.device)
+                num_kv_blocks = int(free * kv_memory_fraction // per_block)
+            else:
+                num_kv_blocks = 512
+            want = (max_batch_tokens + kv_block_size - 1) // kv_block_size + max_batch_size
+            num_kv_blocks = max(min(num_kv_blocks, 8 * want), want)
+        self.kv = KVBlockManager(num_kv_blocks, kv_block_size)
+        self.sched = BatchScheduler(max_batch_size, max_batch_tokens, scheduler, self.kv)
+        shape = (num_kv_blocks, kv_block_size, self.heads_local, self.head_dim)
+        self.k_caches = [torch.zeros(shape, dtype=self.dtype, device=self.device) for _ in m.blocks]
+        self.v_caches = [torch.zeros(shape, dtype=self.dtype, device=self.device) for _ in m.blocks]
+        self.seqs: Dict[int, Sequence] = {}
+        self._next_id = 1
+        self._lock = threading.Lock()
+        self.gen = torch.Generator(device=self.device)
+        self.gen.manual_seed(seed)
+        self.max_context = min(self.cfg.max_position_embeddings, max_batch_tokens)
+        self.stats = {"steps": 0, "prefill_tokens": 0, "decode_tokens": 0, "preemptions": 0}
+        self._scratch = None
+
+    # ---- request API ---------------------------------------------------------------------------------
+    def add_request(self, prompt_ids: List[int], max_tokens: int = 100, temperature: float = 1.0, top_p: float = 1.0,
+                    top_k: int = -1, on_token=None) -> Sequence:
+        if not prompt_ids:
+            prompt_ids = [self.tokenizer.bos_token_id if getattr(self.tokenizer, "bos_token_id", None) is not None else 0]
+        limit = self.cfg.max_position_embeddings
+        if len(prompt_ids) + max_tokens > limit:
+            max_tokens = max(limit - len(prompt_ids), 0)
+        with self._lock:
+            rid = self._next_id
+            self._next_id += 1
+            seq = Sequence(rid, list(prompt_ids), max_tokens, temperature, top_p, top_k, on_token=on_token)
+            if max_tokens <= 0 or not self.sched.add_request(rid, len(prompt_ids), max_tokens):
+                seq.finished, seq.finish_reason = True, "error"
+                seq.done_event.set()
+                return seq
+            self.seqs[rid] = seq
+        return seq
+
+    def has_work(self) -> bool:
+        return self.sched.num_waiting + self.sched.num_running > 0
+
+    # ---- model pieces ----------------------------------------------------------------------------------
+    def _slots(self, rid: int, start: int, count: int) -> torch.Tensor:
+        table = self.kv.block_table(rid)
+        idx = torch.arange(start, start + count)
+        bt = torch.tensor(table, dtype=torch.int64)
+        return (bt[idx // self.block_size] * self.block_size + idx % self.block_size).to(self.device)
+
+    def _rope(self, qkv: torch.Tensor, positions: torch.Tensor) -> torch.Tensor:
+        cos, sin = self.model.rope_tables(self.device)
+        return ops.rope_packed(qkv.clone() if not qkv.is_cuda else qkv, cos, sin, 2 * self.heads_local, self.head_dim,
+                               self.cfg.max_position_embeddings, positions)
+
+    def _layer(self, i: int, blk, x, residual, positions, attn_fn):
+        y, residual = blk.norm1(x, residual)
+        qkv = self._rope(blk.attn.qkv(y), positions)
+        a = attn_fn(i, qkv)
+        y, residual = blk.norm2(blk.attn.out(a), residual)
+        return blk.mlp(y), residual
+
+    @torch.no_grad()
+    def _prefill(self, seq: Sequence) -> torch.Tensor:
+        """Dense causal attention over prompt (+ already generated tokens after a preemption); returns the
+        last position's logits [V]."""
+        ids = seq.all_ids
+        n = len(ids)
+        H, D = self.heads_local, self.head_dim
+        tokens = torch.tensor([ids], dtype=torch.int64, device=self.device)
+        positions = torch.arange(n, dtype=torch.int32, device=self.device)
+        slots = self._slots(seq.req_id, 0, n)
+        m = self.model
+
+        def attn(i, qkv):
+            sops.kv_append(qkv, self.k_caches[i], self.v_caches[i], slots, H, D)
+            v5 = qkv.view(1, n, 3, H, D)
+            o = ops.attention(v5[:, :, 0], v5[:, :, 1], v5[:, :, 2], causal=True)
+            return o.reshape(n, H * D)
+
+        x, residual = m.embed_tokens(tokens), None
+        for i, blk in enumerate(m.blocks):
+            x, residual = self._layer(i, blk, x, residual, positions, attn)
+        y, _ = m.final_norm(x[-1:], residual[-1:] if residual is not None else None)
+        logits = m.lm_head(y) if m.lm_head is not None else ops.linear(y, m.embed.weight)
+        self.stats["prefill_tokens"] += n
+        return logits[0]
+
+    @torch.no_grad()
+    def _decode(self, seqs: List[Sequence]) -> torch.Tensor:
+        """One token for every sequence in ``seqs``; returns logits [B, V]."""
+        B = len(seqs)
+        H, D = self.heads_local, self.head_dim
+        last = [s.all_ids[-1] for s in seqs]
+        ctx = [len(s.all_ids) for s in seqs]               # context length including the token being processed
+        tokens = torch.tensor(last, dtype=torch.int64, device=self.device).view(B, 1)
+        positions = torch.tensor([c - 1 for c in ctx], dtype=torch.int32, device=self.device)
+        tables = [self.kv.block_table(s.req_id) for s in seqs]
+        max_blocks = max(len(t) for t in tables)
+        bt = torch.zeros(B, max_blocks, dtype=torch.int32)
+        for r, t in enumerate(tables):
+            bt[r, :len(t)] = torch.tensor(t, dtype=torch.int32)
+        bt = bt.to(self.device)
+        ctx_t = torch.tensor(ctx, dtype=torch.int32, device=self.device)
+        slots = torch.stack([self._slots(s.req_id, c - 1, 1)[0] for s, c in zip(seqs, ctx)])
+        max_ctx = max(ctx)
+        m = self.model
+
+        def attn(i, qkv):
+            sops.kv_append(qkv, self.k_caches[i], self.v_caches[i], slots, H, D)
+            q = qkv[:, :H * D].reshape(B, H, D)
+            o = sops.paged_attention_decode(q, self.k_caches[i], self.v_caches[i], bt, ctx_t, max_ctx)
+            return o.reshape(B, H * D)
+
+        x, residual = m.embed_tokens(tokens), None
+        for i, blk in enumerate(m.blocks):
+            x, residual = self._layer(i, blk, x, residual, positions, attn)
+        y, _ = m.final_norm(x, residual)
+        logits = m.lm_head(y) if m.lm_head is not None else ops.linear(y, m.embed.weight)
+        self.stats["decode_tokens"] += B
+        return logits
+
+    def _gather_vocab(self, logits: torch.Tensor) -> torch.Tensor:
+        """TP: logits are vocab shards; gather to the full vocabulary (tiny [B, V] all-gather)."""
+        st = self.st
+        if st.tp > 1:
+            import torch.distributed as dist
+            parts = [torch.empty_like(logits) for _ in range(st.tp)]
+            dist.all_gather(parts, logits.contiguous(), group=st.tp_group)
+            logits = torch.cat(parts, dim=-1)
+        return logits[..., :self.cfg.vocab_size]
+
+    def _sample(self, logits: torch.Tensor, seqs: List[Sequence]) -> List[int]:
+        logits = self._gather_vocab(logits)
+        if logits.dim() == 1:
+            logits = logits.unsqueeze(0)
+        logits = logits.contiguous()
+        B = logits.shape[0]
+        t = torch.tensor([s.temperature for s in seqs], dtype=torch.float32, device=self.device)
+        k = torch.tensor([s.top_k for s in seqs], dtype=torch.int32, device=self.device)
+        p = torch.tensor([s.top_p for s in seqs], dtype=torch.float32, device=self.device)
+        u = torch.rand(B, device=self.device, generator=self.gen)
+        if self.st.tp > 1:
+            import torch.distributed as dist
+            dist.broadcast(u, src=self.st.tp_ranks[0], group=self.st.tp_group)   # same draw on every TP rank
+        return sops.sample(logits, t, k, p, u).tolist()    # the step's only D2H copy
+
+    # ---- one engine step ---------------------------------------------------------------------------------
+    def step(self) -> List[Sequence]:
+        """Runs one scheduler step; returns sequences that finished in it."""
+        plan = self.sched.step()
+        if not plan:
+            return []
+        self.stats["steps"] += 1
+        finished: List[Sequence] = []
+        decode = [self.seqs[r] for r, ph, _ in plan if ph == DECODE]
+        for r, ph, _ in plan:
+            if ph == PREFILL:
+                s = self.seqs[r]
+                tok = self._sample(self._prefill(s), [s])[0]
+                self._emit(s, tok, finished)
+        if decode:
+            toks = self._sample(self._decode(decode), decode)
+            for s, tok in zip(decode, toks):
+                self._emit(s, tok, finished)
+        pre = self.sched.pop_preempted()
+        self.stats["preemptions"] += len(pre)
+        return finished
+
+    def _emit(self, s: Sequence, tok: int, finished: List[Sequence]) -> None:
+        if s.finished:
+            return
+        if s.first_token_time is None:
+            s.first_token_time = time.time()
+        s.generated.append(int(tok))
+        if s.on_token is not None:
+            try:
+                s.on_token(s, int(tok))
+            except Exception:  # noqa: BLE001 - a broken stream consumer must not kill the engine
+                pass
+        eos = getattr(self.tokenizer, "eos_token_id", None)
+        if eos is not None and tok == eos:
+            s.finish_reason = "stop"
+        elif len(s.generated) >= s.max_tokens:
+            s.finish_reason = "length"
+        if s.finish_reason:
+            s.finished = True
+            self.sched.finish(s.req_id)
+            self.seqs.pop(s.req_id, None)
+            s.done_event.set()
+            finished.append(s)
+        else:
+            self.sched.on_token(s.req_id)     # grows the KV allocation; may preempt under pressure
+
+    def abort(self, seq: Sequence, reason: str = "error") -> None:
+        if not seq.finished:
+            seq.finished, seq.finish_reason = True, reason
+            self.sched.finish(seq.req_id)
+            self.seqs.pop(seq.req_id, None)
+            seq.done_event.set()
+
+    # ---- convenience: synchronous generation -------------------------------------------------------------
+    def generate(self, prompts: List[List[int]], max_tokens: int = 16, temperature: float = 0.0, top_p: float = 1.0,
+                 top_k: int = -1) -> List[List[int]]:
+        seqs = [self.add_request(p, max_tokens, temperature, top_p, top_k) for p in prompts]
+        while any(not s.finished for s in seqs):
+            if not self.has_work():
+                break
+            self.step()
+        return [s.generated for s in seqs]

@@ -75,6 +75,24 @@ int llmctl_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K,
                      long long ldb, long long ldc, int a_mn, int b_mn, int out_fp32, int beta,
                      int tile_n, int max_ctas, void* stream);
 
+/* ---- K13 / K12 paged KV cache.  Reference: none (server.py:199-204 recomputes the whole sequence). ----
+ * caches: [num_blocks, block_size, heads, head_dim] bf16; slot = block * block_size + offset. */
+int llmctl_kv_append(const void* qkv, long long row_stride, int k_off, int v_off, void* k_cache,
+                     void* v_cache, const long long* slot_mapping, int num_tokens, int heads,
+                     int head_dim, void* stream);
+long long llmctl_paged_attn_scratch_elems(int batch, int heads, int head_dim, int num_splits);
+/* scratch: fp32 [batch * heads * num_splits * (head_dim + 2)] split-K partials. */
+int llmctl_paged_attn_decode(const void* q, long long q_stride, const void* k_cache,
+                             const void* v_cache, const int* block_tables, int max_blocks_per_seq,
+                             const int* context_lens, void* out, long long out_stride, float* scratch,
+                             int batch, int heads, int head_dim, int block_size, int max_context,
+                             int num_splits, float scale, void* stream);
+
+/* ---- K14 sampling.  Reference: per-request Python loop with .item() syncs (server.py:209-235). ---- */
+int llmctl_sample(const void* logits, int logits_is_fp32, long long ld, int rows, int V,
+                  const float* temperature, const int* top_k, const float* top_p, const float* uniform,
+                  long long* out_token, float* out_logprob, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
