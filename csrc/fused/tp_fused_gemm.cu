@@ -1,0 +1,458 @@
+// K1 + K2: tensor/sequence-parallel GEMMs fused with their collective over NVLink peer memory.
+//
+// K1  ag_gemm   : sequence-parallel ALL-GATHER -> column-parallel GEMM in ONE kernel.
+//     Every rank owns rows [r*Ms, (r+1)*Ms) of the activation X[M,K] inside a symmetric buffer Xg (its norm
+//     kernel wrote them there).  CTAs [0, n_copy) are *copy* CTAs: they pull the peers' row blocks into the
+//     local Xg with TMA bulk copies (global(peer) -> smem ring -> global(local)), one peer chunk at a time in
+//     ring order (rank+1, rank+2, ...), and publish chunk_ready[c] when a chunk has landed.  The remaining
+//     CTAs run the tcgen05 GEMM (TMA operands, TMEM accumulators, UMMA 128x256x16): they walk the M chunks
+//     in the same ring order starting with the local one, and the TMA producer warp only waits for
+//     chunk_ready[c] of the chunk it is about to read.  The NVLink transfer of chunk i+1 therefore overlaps the
+//     MMAs of chunk i; the gathered Xg stays materialised for the wgrad GEMM of the backward pass.
+//
+// K2  gemm_rs   : row-parallel GEMM -> sequence-parallel REDUCE-SCATTER in ONE kernel.
+//     Partial sums D[M,N] = X[M,Kl] Wl^T are produced tile by tile; the epilogue converts each 128-row slab to
+//     bf16 and stores it straight into the OWNER rank's staging slot  stage[src_rank][Ms, N]  with 16-byte
+//     P2P stores while the tensor core is already working on the next tile (TMEM double buffering).  Tiles
+//     are visited destination by destination (rank+1, ..., rank last); when the last tile for a destination has
+//     been pushed, that destination's flag is raised.  The owner's follow-up kernel
+//     (llmctl_rs_reduce_rmsnorm, below) sums the `world` slots in fp32 in rank order — deterministic, no
+//     atomics — fused with the residual add and the RMSNorm that sits on the sequence shard (K3).
+//
+// Reference: no TP/SP exists in the reference (planner integers only: reference
+// llmctl/cli/commands/plan.py:79-80,110-113; `sequence_parallel` flag: configs/presets/llama-7b-a100x8.toml:36).
+// Baseline to beat: NCCL all-gather + cuBLAS, cuBLAS + NCCL reduce-scatter, run back to back.
+#include "../comm/symm.cuh"
+#include "../common/tma_host.h"
+#include "../common/util.cuh"
+
+namespace llmctl {
+using namespace ptx;
+using namespace symm;
+
+constexpr int kFBM = 128, kFBN = 256, kFBK = 64;
+constexpr int kFStages = 4;
+constexpr int kFABytes = kFBM * kFBK * 2;
+constexpr int kFBBytes = kFBN * kFBK * 2;
+constexpr int kFStageBytes = kFABytes + kFBBytes;
+constexpr int kFSmem = kFStages * kFStageBytes + 1024;
+constexpr int kFThreads = 192;
+constexpr int kCopyPiece = 32768;            // bytes per TMA bulk copy
+constexpr int kCopyStages = 4;               // smem ring of the copy CTAs (4 x 32 KB)
+
+__device__ __forceinline__ void bulk_store_1d(void* gdst, const void* smem_src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(
+                   reinterpret_cast<uint64_t>(gdst)),
+               "r"(smem_u32(smem_src)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void st_release_gpu(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+struct FusedArgs {
+  int M, N, K;
+  int rank, world;
+  int rows_per_rank;          // Ms = M / world
+  uint32_t epoch;
+  int n_copy;                 // K1: number of copy CTAs (0 for K2)
+};
+
+// --------------------------------------------------------------------------------------------------
+// Shared GEMM core (1-CTA, 128 x 256 tile).  kMode 1 = K1 (wait for chunk_ready before loading A),
+// kMode 2 = K2 (epilogue pushes bf16 tiles to the owner's staging slot).
+// Tiles are enumerated chunk-major: chunk i covers M rows of rank c_i = (rank + i [+1 for K2]) % world.
+// --------------------------------------------------------------------------------------------------
+template <int kMode>
+__global__ void __launch_bounds__(kFThreads, 1)
+tp_fused_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                     __nv_bfloat16* __restrict__ C, long long ldc, FusedArgs a,
+                     PeerTable xg,                 // K1: symmetric Xg (per-rank base);  K2: staging buffers
+                     PeerTable pads, uint32_t* __restrict__ local_flags /* chunk_ready / counters */) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint64_t bar_full[kFStages];
+  __shared__ uint64_t bar_empty[kFStages];
+  __shared__ uint64_t bar_tfull[2];
+  __shared__ uint64_t bar_tempty[2];
+  __shared__ uint64_t bar_copy[kCopyStages];
+  __shared__ uint32_t tmem_base_smem;
+
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem = smem_raw + (smem_base - smem_u32(smem_raw));
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int Ms = a.rows_per_rank;
+
+  // ================================ K1 copy CTAs ================================
+  if (kMode == 1 && static_cast<int>(blockIdx.x) < a.n_copy) {
+    if (threadIdx.x == 0) {
+      for (int i = 0; i < kCopyStages; ++i) mbar_init(&bar_copy[i], 1);
+      fence_mbar_init();
+      // announce that this rank's own rows are in place (written by the previous kernel on this stream)
+      if (blockIdx.x == 0)
+        for (int p = 0; p < a.world; ++p)
+          signal_set(reinterpret_cast<uint32_t*>(pads.ptr[p]) + a.rank, a.epoch);
+      const long long chunk_bytes = static_cast<long long>(Ms) * a.K * 2;
+      const int pieces = static_cast<int>((chunk_bytes + kCopyPiece - 1) / kCopyPiece);
+      uint32_t phase_bits = 0;
+      int issued = 0;       // pieces issued by this CTA (ring position)
+      for (int i = 1; i < a.world; ++i) {
+        const int src = (a.rank + i) % a.world;
+        signal_wait_ge(reinterpret_cast<const uint32_t*>(pads.ptr[a.rank]) + src, a.epoch);
+        const uint8_t* gsrc = reinterpret_cast<const uint8_t*>(xg.ptr[src]) + static_cast<long long>(src) * chunk_bytes;
+        uint8_t* gdst = reinterpret_cast<uint8_t*>(xg.ptr[a.rank]) + static_cast<long long>(src) * chunk_bytes;
+        // software pipeline over this CTA's pieces: keep up to kCopyStages loads in flight
+        int head = blockIdx.x, tail = blockIdx.x;     // piece indices (stride n_copy)
+        int in_flight = 0;
+        while (tail < pieces) {
+          while (head < pieces && in_flight < kCopyStages) {
+            const int slot = issued % kCopyStages;
+            tma_store_wait_read<0>();   // every earlier smem->global store has finished READING its slot
+            const long long off = static_cast<long long>(head) * kCopyPiece;
+            const uint32_t bytes = static_cast<uint32_t>(min(static_cast<long long>(kCopyPiece), chunk_bytes - off));
+            mbar_expect_tx(&bar_copy[slot], bytes);
+            bulk_load_1d(smem + slot * kCopyPiece, gsrc + off, bytes, &bar_copy[slot]);
+            ++issued; ++in_flight; head += a.n_copy;
+          }
+          const int slot = (issued - in_flight) % kCopyStages;
+          mbar_wait(&bar_copy[slot], (phase_bits >> slot) & 1u);
+          phase_bits ^= (1u << slot);
+          const long long off = static_cast<long long>(tail) * kCopyPiece;
+          const uint32_t bytes = static_cast<uint32_t>(min(static_cast<long long>(kCopyPiece), chunk_bytes - off));
+          fence_proxy_async_smem();
+          bulk_store_1d(gdst + off, smem + slot * kCopyPiece, bytes);
+          tma_store_commit();
+          --in_flight; tail += a.n_copy;
+        }
+        tma_store_wait<0>();                             // this CTA's part of chunk `src` is in local memory
+        __threadfence();
+        // last copy CTA to finish the chunk publishes it
+        const uint32_t done = atomicAdd(&local_flags[16 + src], 1u) + 1u;
+        if (done == static_cast<uint32_t>(a.n_copy)) {
+          atomicExch(&local_flags[16 + src], 0u);
+          st_release_gpu(&local_flags[src], a.epoch);
+        }
+      }
+    }
+    return;
+  }
+
+  // ================================ GEMM CTAs ================================
+  const int cta = (kMode == 1) ? static_cast<int>(blockIdx.x) - a.n_copy : static_cast<int>(blockIdx.x);
+  const int n_cta = (kMode == 1) ? static_cast<int>(gridDim.x) - a.n_copy : static_cast<int>(gridDim.x);
+  const int m_per_chunk = (Ms + kFBM - 1) / kFBM;
+  const int num_n = (a.N + kFBN - 1) / kFBN;
+  const int tiles_per_chunk = m_per_chunk * num_n;
+  const int num_tiles = tiles_per_chunk * a.world;
+  const int num_kb = (a.K + kFBK - 1) / kFBK;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < kFStages; ++i) {
+      mbar_init(&bar_full[i], 1);
+      mbar_init(&bar_empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&bar_tfull[i], 1);
+      mbar_init(&bar_tempty[i], 4);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmA);
+    prefetch_tmap(&tmB);
+  }
+  if (warp == 1) tmem_alloc<1>(&tmem_base_smem, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_smem;
+
+  // tile -> (chunk rank, m0 in global rows, n0)
+  auto decode = [&](int tile, int& crank, int& m0, int& n0, int& m_end) {
+    const int ci = tile / tiles_per_chunk;
+    const int t = tile % tiles_per_chunk;
+    crank = (a.rank + ci + (kMode == 2 ? 1 : 0)) % a.world;
+    m0 = crank * Ms + (t % m_per_chunk) * kFBM;
+    n0 = (t / m_per_chunk) * kFBN;
+    m_end = (crank + 1) * Ms;
+  };
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int ready_chunk = -1;
+      for (int tile = cta; tile < num_tiles; tile += n_cta) {
+        int crank, m0, n0, m_end;
+        decode(tile, crank, m0, n0, m_end);
+        if (kMode == 1 && crank != a.rank && crank != ready_chunk) {
+          while (static_cast<int32_t>(ld_acquire_gpu(&local_flags[crank]) - a.epoch) < 0) __nanosleep(64);
+          fence_proxy_async_all();      // generic-proxy flag read -> async-proxy (TMA) data reads
+          ready_chunk = crank;
+        }
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&bar_empty[stage], phase ^ 1u);
+          uint8_t* sA = smem + stage * kFStageBytes;
+          uint8_t* sB = sA + kFABytes;
+          mbar_expect_tx(&bar_full[stage], kFStageBytes);
+          tma_load_2d(sA, &tmA, &bar_full[stage], kb * kFBK, m0);
+          tma_load_2d(sB, &tmB, &bar_full[stage], kb * kFBK, n0);
+          if (++stage == kFStages) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(kFBM, kFBN, 0u, 0u);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t aphase = 0;
+      for (int tile = cta; tile < num_tiles; tile += n_cta) {
+        mbar_wait(&bar_tempty[acc], aphase ^ 1u);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * kFBN);
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&bar_full[stage], phase);
+          tc_fence_after();
+          const uint32_t a_addr = smem_base + stage * kFStageBytes;
+          const uint32_t b_addr = a_addr + kFABytes;
+#pragma unroll
+          for (int k = 0; k < kFBK / 16; ++k)
+            umma_ss<1>(d_tmem, make_smem_desc(a_addr + k * 32, 16, 1024, 2),
+                       make_smem_desc(b_addr + k * 32, 16, 1024, 2), idesc, (kb | k) != 0 ? 1u : 0u);
+          umma_commit<1>(&bar_empty[stage]);
+          if (++stage == kFStages) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+        umma_commit<1>(&bar_tfull[acc]);
+        acc ^= 1;
+        if (acc == 0) aphase ^= 1u;
+      }
+    }
+  } else {
+    const int q = warp & 3;
+    int acc = 0;
+    uint32_t aphase = 0;
+    for (int tile = cta; tile < num_tiles; tile += n_cta) {
+      int crank, m0, n0, m_end;
+      decode(tile, crank, m0, n0, m_end);
+      mbar_wait(&bar_tfull[acc], aphase);
+      tc_fence_after();
+      const int row = m0 + q * 32 + lane;
+      const bool row_ok = row < m_end && row < a.M;
+      const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(acc * kFBN);
+      __nv_bfloat16* crow;
+      if (kMode == 2) {
+        // owner's staging slot for this source rank: stage[rank][Ms, N]; row index local to the owner
+        __nv_bfloat16* base = reinterpret_cast<__nv_bfloat16*>(xg.ptr[crank]) +
+                              static_cast<long long>(a.rank) * Ms * a.N;
+        crow = base + static_cast<long long>(row - crank * Ms) * a.N + n0;
+      } else {
+        crow = C + static_cast<long long>(row) * ldc + n0;
+      }
+#pragma unroll 1
+      for (int c = 0; c < kFBN / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_x32(t_row + c * 32, r);
+        tmem_ld_wait();
+        if (row_ok) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int col = n0 + c * 32 + j * 8;
+            if (col < a.N) {
+              float f[8];
+#pragma unroll
+              for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(r[j * 8 + e]);
+              const bf16x8 pk = pack8(f);
+              if (kMode == 2) st_v4(crow + c * 32 + j * 8, *reinterpret_cast<const uint4*>(&pk));
+              else store8(crow + c * 32 + j * 8, pk);
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (kMode == 2) {
+        // count finished (tile, warp) pairs per destination; the last one raises the destination's flag
+        __threadfence_system();
+        if (lane == 0) {
+          const uint32_t done = atomicAdd(&local_flags[crank], 1u) + 1u;
+          if (done == static_cast<uint32_t>(tiles_per_chunk * 4)) {
+            atomicExch(&local_flags[crank], 0u);
+            signal_set(reinterpret_cast<uint32_t*>(pads.ptr[crank]) + 8 + a.rank, a.epoch);
+          }
+        }
+      }
+      if (lane == 0) mbar_arrive(&bar_tempty[acc]);
+      acc ^= 1;
+      if (acc == 0) aphase ^= 1u;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<1>(tmem_base, 512);
+  }
+}
+
+// --------------------------------------------------------------------------------------------------
+// K2 consumer / K3 on the sequence shard: out rows = sum over source ranks of stage[s] (+ residual), RMSNorm.
+// One warp per row (cols <= 8192), fp32 accumulation in rank order.
+// --------------------------------------------------------------------------------------------------
+template <int kMaxVec>
+__global__ void __launch_bounds__(128)
+rs_reduce_rmsnorm_kernel(const __nv_bfloat16* __restrict__ stage, PeerTable pads, int rank, int world,
+                         const __nv_bfloat16* __restrict__ residual, const __nv_bfloat16* __restrict__ w,
+                         __nv_bfloat16* __restrict__ h_out, __nv_bfloat16* __restrict__ y, float* __restrict__ rstd_out,
+                         int rows, int cols, float eps, uint32_t epoch) {
+  // wait until every source rank has pushed all its tiles for us
+  if (threadIdx.x < world)
+    signal_wait_ge(reinterpret_cast<const uint32_t*>(pads.ptr[rank]) + 8 + threadIdx.x, epoch);
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  const int row = blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int nvec = cols >> 3;
+  const long long slot = static_cast<long long>(rows) * cols;
+  float acc[kMaxVec][8];
+  float ss = 0.f;
+#pragma unroll
+  for (int i = 0; i < kMaxVec; ++i) {
+    const int v = i * 32 + lane;
+    if (v < nvec) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+      for (int s = 0; s < world; ++s) {
+        float f[8];
+        unpack8(load8(stage + s * slot + static_cast<long long>(row) * cols + v * 8), f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i][j] += f[j];
+      }
+      if (residual != nullptr) {
+        float f[8];
+        unpack8(load8(residual + static_cast<long long>(row) * cols + v * 8), f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i][j] += f[j];
+      }
+      const bf16x8 hq = pack8(acc[i]);
+      if (h_out != nullptr) store8(h_out + static_cast<long long>(row) * cols + v * 8, hq);
+      unpack8(hq, acc[i]);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) ss += acc[i][j] * acc[i][j];
+    }
+  }
+  ss = warp_sum(ss);
+  const float rstd = rsqrtf(ss / cols + eps);
+  if (lane == 0 && rstd_out) rstd_out[row] = rstd;
+  if (y == nullptr) return;
+#pragma unroll
+  for (int i = 0; i < kMaxVec; ++i) {
+    const int v = i * 32 + lane;
+    if (v < nvec) {
+      float g[8], o[8];
+      unpack8(load8(w + v * 8), g);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = acc[i][j] * rstd * g[j];
+      store8(y + static_cast<long long>(row) * cols + v * 8, pack8(o));
+    }
+  }
+}
+
+static int fused_num_sms() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+      n = kNumSMs;
+  }
+  return n;
+}
+
+}  // namespace llmctl
+
+using namespace llmctl;
+
+// K1.  xg: symmetric activation buffer [M, K] bf16 on every rank (rank r's rows [r*Ms,(r+1)*Ms) valid on entry,
+// all rows valid locally on exit).  W: [N, K] local weight shard.  C: [M, N] local output.
+// local_flags: 32 zero-initialised uint32 in local device memory (reused across calls).
+// pads slots [0, world) are used.  epoch must increase by 1 per call on every rank.
+LLMCTL_API int llmctl_ag_gemm(llmctl::symm::PeerTable xg, const void* W, void* C, int M, int N, int K,
+                              long long ldw, long long ldc, llmctl::symm::PeerTable pads,
+                              unsigned int* local_flags, int rank, int world, unsigned int epoch,
+                              int n_copy, void* stream) {
+  LLMCTL_BEGIN();
+  LLMCTL_REQUIRE(world >= 1 && world <= symm::kMaxRanks && M % world == 0 && K % 8 == 0 && N % 8 == 0);
+  LLMCTL_REQUIRE((static_cast<long long>(M / world) * K * 2) % 16 == 0);
+  CUtensorMap tmA, tmB;
+  int rc = get_tmap_2d_bf16(&tmA, xg.ptr[rank], M, K, K, kFBM, kFBK, 1);
+  if (rc) LLMCTL_FAIL(rc, "tensor map A");
+  rc = get_tmap_2d_bf16(&tmB, W, N, K, ldw, kFBN, kFBK, 1);
+  if (rc) LLMCTL_FAIL(rc, "tensor map B");
+  auto kern = tp_fused_gemm_kernel<1>;
+  LLMCTL_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kFSmem));
+  if (world == 1) n_copy = 0;
+  else if (n_copy <= 0) n_copy = 12;
+  FusedArgs a{M, N, K, rank, world, M / world, epoch, n_copy};
+  const int grid = fused_num_sms();
+  kern<<<grid, kFThreads, kFSmem, (cudaStream_t)stream>>>(tmA, tmB, (__nv_bfloat16*)C, ldc, a, xg, pads,
+                                                          local_flags);
+  LLMCTL_RETURN_LAST();
+}
+
+// K2.  X: [M, K] local activation (K = local shard of the contraction dim), W: [N, K] local weight shard.
+// stage: symmetric staging buffer [world, Ms, N] bf16 on every rank (slot s receives rank s's partial rows).
+// pads slots [8, 8 + world) are used.  local_flags: 32 zero-initialised uint32 (tile counters).
+LLMCTL_API int llmctl_gemm_rs(const void* X, const void* W, llmctl::symm::PeerTable stage, int M, int N, int K,
+                              long long ldx, long long ldw, llmctl::symm::PeerTable pads,
+                              unsigned int* local_flags, int rank, int world, unsigned int epoch,
+                              void* stream) {
+  LLMCTL_BEGIN();
+  LLMCTL_REQUIRE(world >= 1 && world <= symm::kMaxRanks && M % world == 0 && K % 8 == 0 && N % 8 == 0);
+  CUtensorMap tmA, tmB;
+  int rc = get_tmap_2d_bf16(&tmA, X, M, K, ldx, kFBM, kFBK, 1);
+  if (rc) LLMCTL_FAIL(rc, "tensor map A");
+  rc = get_tmap_2d_bf16(&tmB, W, N, K, ldw, kFBN, kFBK, 1);
+  if (rc) LLMCTL_FAIL(rc, "tensor map B");
+  auto kern = tp_fused_gemm_kernel<2>;
+  LLMCTL_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kFSmem));
+  FusedArgs a{M, N, K, rank, world, M / world, epoch, 0};
+  const int Ms = M / world;
+  const int tiles = ((Ms + kFBM - 1) / kFBM) * ((N + kFBN - 1) / kFBN) * world;
+  int grid = fused_num_sms();
+  if (tiles < grid) grid = tiles;
+  kern<<<grid, kFThreads, kFSmem, (cudaStream_t)stream>>>(tmA, tmB, nullptr, 0, a, stage, pads, local_flags);
+  LLMCTL_RETURN_LAST();
+}
+
+// out[rows, cols] = sum_s stage[s] (+ residual); y = rmsnorm(out) * w.  rows = Ms.  Waits for the K2 flags of
+// `epoch`.  h_out / residual / y / rstd may be NULL (y == NULL: reduce only).
+LLMCTL_API int llmctl_rs_reduce_rmsnorm(const void* stage_local, llmctl::symm::PeerTable pads, int rank,
+                                        int world, const void* residual, const void* w, void* h_out, void* y,
+                                        float* rstd, int rows, int cols, float eps, unsigned int epoch,
+                                        void* stream) {
+  LLMCTL_BEGIN();
+  LLMCTL_REQUIRE(cols % 8 == 0 && cols <= 8192 && world >= 1 && world <= symm::kMaxRanks);
+  if (rows == 0) return 0;
+  cudaStream_t s = (cudaStream_t)stream;
+  const int per_lane = ((cols >> 3) + 31) / 32;
+  dim3 grid((rows + 3) / 4);
+#define LAUNCH(MV)                                                                                          \
+  rs_reduce_rmsnorm_kernel<MV><<<grid, 128, 0, s>>>((const __nv_bfloat16*)stage_local, pads, rank, world,   \
+                                                    (const __nv_bfloat16*)residual, (const __nv_bfloat16*)w, \
+                                                    (__nv_bfloat16*)h_out, (__nv_bfloat16*)y, rstd, rows, cols, eps, epoch)
+  if (per_lane <= 4) LAUNCH(4);
+  else if (per_lane <= 8) LAUNCH(8);
+  else if (per_lane <= 16) LAUNCH(16);
+  else LAUNCH(32);
+#undef LAUNCH
+  LLMCTL_RETURN_LAST();
+}

@@ -1,15 +1,192 @@
-"""Fused compute + collective paths over NVLink peer memory (K1 ag_gemm, K2 gemm_rs, K7 rs_adam, K11
-ar_rmsnorm).  ``enabled(x)`` gates the fused TP/SP linears: CUDA bf16 tensors, symmetric-memory workspace
-initialised for the TP group, and the native symbols present.  Everything else uses the NCCL/gloo
-collectives in ``parallel/tp.py`` (baseline + CPU path).
+"""Fused compute + collective paths over NVLink peer memory for tensor / sequence parallelism:
+K1 ``ag_gemm`` (all-gather -> column-parallel GEMM), K2 ``gemm_rs`` (row-parallel GEMM -> reduce-scatter,
+finished by ``rs_reduce_rmsnorm`` on the sequence shard) and K11 ``ar_residual_rmsnorm`` (decode).
+
+``TPFusedContext`` owns the symmetric workspaces of one TP group: two alternating activation buffers
+``Xg[M, K]`` for K1 (the producer norm writes this rank's rows straight into them), two alternating staging
+buffers ``stage[world, M/world, N]`` for K2, the signal pads and the per-call epochs.  ``enabled(x)`` gates the
+fused linears in ``parallel/tp.py``; anything unsupported falls back to the NCCL collectives there
+(baseline path, also the CPU/gloo path).
 
 Reference: ``llmctl.comms`` is an empty package (reference llmctl/comms/__init__.py).
 """
 from __future__ import annotations
 
-import torch
+import ctypes
+from typing import Optional
 
-_ctx = None   # set by comms.symm.init_tp_workspace()
+import torch
+import torch.distributed as dist
+
+from ..ops import functional as ops
+from ..ops import native
+from .symm import PeerTable, SymmBuffer
+
+_ctx: Optional["TPFusedContext"] = None
+
+vp, i32, i64, f32, u32 = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_float, ctypes.c_uint
+native.register_signature("llmctl_ag_gemm", [PeerTable, vp, vp, i32, i32, i32, i64, i64, PeerTable, vp, i32, i32, u32, i32, vp])
+native.register_signature("llmctl_gemm_rs", [vp, vp, PeerTable, i32, i32, i32, i64, i64, PeerTable, vp, i32, i32, u32, vp])
+native.register_signature("llmctl_rs_reduce_rmsnorm", [vp, PeerTable, i32, i32, vp, vp, vp, vp, vp, i32, i32, f32, u32, vp])
+native.register_signature("llmctl_ar_residual_rmsnorm", [PeerTable, i64, vp, PeerTable, i32, i32, i32, vp, vp, vp, vp, i32, i32, f32, u32, vp])
+
+
+class TPFusedContext:
+    def __init__(self, group, rank: int, world: int, max_tokens: int, hidden: int, max_n: int, device: torch.device):
+        self.group, self.rank, self.world, self.device = group, rank, world, device
+        self.max_tokens, self.hidden = max_tokens, hidden
+        # K1: gathered activations [M, K<=hidden]; K2: staging [world, M/world, N<=hidden]  (both M*hidden bf16)
+        self.xg = [SymmBuffer(max_tokens * hidden, torch.bfloat16, group, device) for _ in range(2)]
+        self.stage = [SymmBuffer(max_tokens * hidden, torch.bfloat16, group, device) for _ in range(2)]
+        self.flags_ag = torch.zeros(32, dtype=torch.int32, device=device)
+        self.flags_rs = torch.zeros(32, dtype=torch.int32, device=device)
+        # one epoch counter per kernel family (NOT per buffer): the local chunk_ready flags are shared by both
+        # alternating buffers, so epochs must keep increasing across them
+        self.ep_ag = 0
+        self.ep_rs = 0
+        self.i_ag = 0
+        self.i_rs = 0
+        self.n_copy = 12
+        torch.cuda.synchronize(device)
+        self.xg[0].barrier()
+
+    def usable(self, x: torch.Tensor) -> bool:
+        return (ops.kernel_config().gemm == "native" and x.dim() == 2 and x.shape[0] * self.world <= self.max_tokens
+                and x.shape[1] <= self.hidden * 4)
+
+    # ---- K1 ------------------------------------------------------------------------------------------
+    def next_xg(self, rows_local: int, cols: int):
+        """The buffer the *producer* (norm) must write this rank's rows into for the next ag_linear."""
+        buf = self.xg[self.i_ag]
+        M = rows_local * self.world
+        full = buf.tensor[:M * cols].view(M, cols)
+        return buf, full, full[self.rank * rows_local:(self.rank + 1) * rows_local]
+
+    def ag_gemm(self, x_local: torch.Tensor, w: torch.Tensor):
+        """x_local [Ms, K] (copied into the symmetric buffer unless it already lives there) -> (y [M, N], Xg [M, K])."""
+        Ms, K = x_local.shape
+        N = w.shape[0]
+        buf, full, mine = self.next_xg(Ms, K)
+        if x_local.data_ptr() != mine.data_ptr():
+            mine.copy_(x_local)
+        M = Ms * self.world
+        self.ep_ag += 1
+        y = torch.empty(M, N, dtype=torch.bfloat16, device=x_local.device)
+        native.call("llmctl_ag_gemm", buf.peers, w.data_ptr(), y.data_ptr(), M, N, K, w.stride(0), y.stride(0),
+                    buf.pads, self.flags_ag.data_ptr(), self.rank, self.world, self.ep_ag, self.n_copy,
+                    native.stream_ptr())
+        self.i_ag ^= 1
+        return y, full
+
+    # ---- K2 ------------------------------------------------------------------------------------------
+    def gemm_rs(self, x: torch.Tensor, w: torch.Tensor, residual: Optional[torch.Tensor] = None,
+                norm_w: Optional[torch.Tensor] = None, eps: float = 1e-5):
+        """x [M, Kl], w [N, Kl] -> reduce-scattered rows [M/world, N] (+ residual).  With ``norm_w`` also returns
+        rmsnorm(rows) * norm_w and rstd.  Returns (h, y, rstd)."""
+        M, Kl = x.shape
+        N = w.shape[0]
+        Ms = M // self.world
+        buf = self.stage[self.i_rs]
+        self.ep_rs += 1
+        ep = self.ep_rs
+        native.call("llmctl_gemm_rs", x.data_ptr(), w.data_ptr(), buf.peers, M, N, Kl, x.stride(0), w.stride(0), buf.pads,
+                    self.flags_rs.data_ptr(), self.rank, self.world, ep, native.stream_ptr())
+        h = torch.empty(Ms, N, dtype=torch.bfloat16, device=x.device)
+        y = torch.empty_like(h) if norm_w is not None else None
+        rstd = torch.empty(Ms, dtype=torch.float32, device=x.device) if norm_w is not None else None
+        native.call("llmctl_rs_reduce_rmsnorm", buf.tensor.data_ptr(), buf.pads, self.rank, self.world,
+                    native.ptr(residual), native.ptr(norm_w), h.data_ptr(), native.ptr(y), native.ptr(rstd), Ms, N,
+                    float(eps), ep, native.stream_ptr())
+        self.i_rs ^= 1
+        return h, y, rstd
+
+
+class _AGLinearFn(torch.autograd.Function):
+    """y = all_gather(x_local) @ w.T (K1).  Backward: dgrad = K2 (GEMM -> reduce-scatter), wgrad on the gathered
+    activation the forward kernel left behind."""
+
+    @staticmethod
+    def forward(ctx, x_local, w):
+        y, xg_full = _ctx.ag_gemm(x_local, w)
+        ctx.save_for_backward(xg_full.clone() if _ctx.world > 1 else xg_full, w)   # Xg is recycled two calls later
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        xg, w = ctx.saved_tensors
+        dy = dy if dy.is_contiguous() else dy.contiguous()
+        # dX_full = dy @ w  -> reduce-scatter over tokens.  K2 expects the weight as [N_out, K]: here the "weight"
+        # is w^T ([K_in, N_local]); use the transposed copy kept on the parameter (built lazily, refreshed per step)
+        wt = _transposed(w)
+        h, _, _ = _ctx.gemm_rs(dy, wt)
+        mg = getattr(w, "main_grad", None)
+        if mg is not None:
+            fresh = getattr(w, "_main_grad_fresh", False)
+            ops.gemm_raw(dy, xg, a_mn=True, b_mn=True, out=mg, accumulate=not fresh)
+            w._main_grad_fresh = False
+            cb = getattr(w, "_grad_ready_cb", None)
+            if cb is not None:
+                cb(w)
+            return h, None
+        return h, ops.gemm_raw(dy, xg, a_mn=True, b_mn=True)
+
+
+class _LinearRSFn(torch.autograd.Function):
+    """h_local = reduce_scatter(x @ w.T) (K2).  Backward: dX = all_gather(dh) @ w  (K1 with w^T), wgrad on it."""
+
+    @staticmethod
+    def forward(ctx, x, w):
+        h, _, _ = _ctx.gemm_rs(x, w)
+        ctx.save_for_backward(x, w)
+        return h
+
+    @staticmethod
+    def backward(ctx, dh):
+        x, w = ctx.saved_tensors
+        dh = dh if dh.is_contiguous() else dh.contiguous()
+        wt = _transposed(w)                         # [K_local, N]: acts as the [N_out=K_local, K=N] weight of K1
+        dx, dh_full = _ctx.ag_gemm(dh, wt)
+        mg = getattr(w, "main_grad", None)
+        if mg is not None:
+            fresh = getattr(w, "_main_grad_fresh", False)
+            ops.gemm_raw(dh_full, x, a_mn=True, b_mn=True, out=mg, accumulate=not fresh)
+            w._main_grad_fresh = False
+            cb = getattr(w, "_grad_ready_cb", None)
+            if cb is not None:
+                cb(w)
+            return dx, None
+        return dx, ops.gemm_raw(dh_full, x, a_mn=True, b_mn=True)
+
+
+def _transposed(w: torch.Tensor) -> torch.Tensor:
+    """w^T as a contiguous tensor, cached on the parameter and refreshed when the parameter version changes."""
+    from ..parallel.zero import PARAM_GENERATION
+    ver = (w._version, PARAM_GENERATION[0])
+    cached = getattr(w, "_wt_cache", None)
+    if cached is None or cached[0] != ver or cached[1].data_ptr() == 0:
+        w._wt_cache = (ver, w.detach().t().contiguous())
+    return w._wt_cache[1]
+
+
+def init_tp_workspace(max_tokens: int, hidden: int, max_n: Optional[int] = None) -> Optional[TPFusedContext]:
+    """Create the fused TP/SP context for the current mesh (no-op unless CUDA + NCCL + tp > 1 + SP)."""
+    global _ctx
+    from . import symm
+    from .mesh import get_state
+    st = get_state()
+    if st.tp <= 1 or not st.sequence_parallel or st.device.type != "cuda" or not symm.available():
+        _ctx = None
+        return None
+    if not native.has_symbol("llmctl_ag_gemm"):
+        _ctx = None
+        return None
+    _ctx = TPFusedContext(st.tp_group, st.tp_rank, st.tp, max_tokens, hidden, max_n or hidden, st.device)
+    return _ctx
+
+
+def shutdown() -> None:
+    global _ctx
+    _ctx = None
 
 
 def enabled(x: torch.Tensor) -> bool:
@@ -17,8 +194,8 @@ def enabled(x: torch.Tensor) -> bool:
 
 
 def ag_linear(x: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
-    return _ctx.ag_linear(x, w)
+    return _AGLinearFn.apply(x, w)
 
 
 def linear_rs(x: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
-    return _ctx.linear_rs(x, w)
+    return _LinearRSFn.apply(x, w)

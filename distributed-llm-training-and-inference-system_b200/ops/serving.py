@@ -73,7 +73,7 @@ def paged_attention_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torc
 def sample_reference(logits: torch.Tensor, temperature: float, top_k: int, top_p: float,
                      generator: Optional[torch.Generator] = None) -> int:
     """The reference's sampling pipeline for one row (reference llmctl/serve/server.py:209-235), restated."""
-    x = logits.float()
+    x = logits.float().clone()      # never edit the caller's logits
     if temperature <= 0:
         return int(x.argmax())
     if temperature != 1.0:

@@ -36,6 +36,10 @@ from ..ops import optim as fused_optim
 
 _ALIGN = 128  # elements; keeps every parameter view 256-byte aligned (TMA needs 16)
 
+#: bumped by every optimizer step; caches derived from parameter values (e.g. transposed weights) key on it,
+#: because the fused kernels update parameters through raw pointers and never touch tensor._version
+PARAM_GENERATION = [0]
+
 
 def _round_up(x: int, m: int) -> int:
     return (x + m - 1) // m * m
@@ -44,7 +48,8 @@ def _round_up(x: int, m: int) -> int:
 class ParamUnit:
     """One reduction / gather bucket."""
 
-    def __init__(self, name: str, module: nn.Module, st: ParallelState, zero_stage: int, grad_dtype: torch.dtype):
+    def __init__(self, name: str, module: nn.Module, st: ParallelState, zero_stage: int, grad_dtype: torch.dtype,
+                 param_storage: Optional[torch.Tensor] = None, grad_storage: Optional[torch.Tensor] = None):
         self.name, self.module, self.st = name, module, st
         self.zero_stage = zero_stage
         self.grad_dtype = grad_dtype
@@ -72,7 +77,12 @@ class ParamUnit:
         self.shard_hi = self.shard_lo + self.shard_numel
 
         # ---- parameters -> flat buffer -------------------------------------------------------
-        flat = torch.zeros(self.numel, dtype=self.dtype, device=self.device)
+        if param_storage is not None:
+            flat = param_storage[:self.numel]
+            flat.zero_()
+        else:
+            flat = torch.zeros(self.numel, dtype=self.dtype, device=self.device)
+        self._persistent_grad = grad_storage
         for p, o in zip(self.params, self.offsets):
             flat[o:o + p.numel()].copy_(p.data.reshape(-1))
         self.flat_param: Optional[torch.Tensor] = flat
@@ -130,7 +140,10 @@ class ParamUnit:
     # ---- gradient bucket -----------------------------------------------------------------------
     def ensure_grad_bucket(self) -> None:
         if self.flat_grad is None:
-            self.flat_grad = torch.empty(self.numel, dtype=self.grad_dtype, device=self.device)
+            if self._persistent_grad is not None:
+                self.flat_grad = self._persistent_grad[:self.numel]
+            else:
+                self.flat_grad = torch.empty(self.numel, dtype=self.grad_dtype, device=self.device)
             for lo, hi in self.gaps:
                 self.flat_grad[lo:hi].zero_()
             self._pending = len(self.params)
@@ -166,7 +179,7 @@ class ZeroOptimizer:
     def __init__(self, model: nn.Module, *, lr: float = 2e-4, betas=(0.9, 0.95), eps: float = 1e-8,
                  weight_decay: float = 0.1, zero_stage: int = 0, grad_clip: float = 1.0,
                  grad_dtype: Optional[torch.dtype] = None, units: Optional[Sequence] = None,
-                 state: Optional[ParallelState] = None):
+                 state: Optional[ParallelState] = None, comm: str = "auto"):
         self.st = state or get_state()
         self.model = model
         self.lr, self.betas, self.eps, self.weight_decay = lr, betas, eps, weight_decay
@@ -178,13 +191,25 @@ class ZeroOptimizer:
         first = next(p for p in model.parameters() if p.requires_grad)
         self.grad_dtype = grad_dtype or (torch.float32 if first.dtype == torch.float32 else torch.bfloat16)
         named = units if units is not None else default_units(model)
+        named = [(n, m) for n, m in named if any(p.requires_grad for p in m.parameters())]
         self.units: List[ParamUnit] = []
+        self.native_comm = self._init_native_comm(named, comm)
+        off = 0
         for name, mod in named:
-            if any(p.requires_grad for p in mod.parameters()):
-                u = ParamUnit(name, mod, self.st, self.zero_stage, self.grad_dtype)
-                u._on_ready = self._unit_ready
-                self.units.append(u)
+            ps = gs = None
+            if self.native_comm is not None:
+                n = _unit_numel(mod, self.st.dp)
+                ps = self.native_comm["params"].tensor[off:off + n]
+                gs = self.native_comm["grads"].tensor[off:off + n]
+            u = ParamUnit(name, mod, self.st, self.zero_stage, self.grad_dtype, ps, gs)
+            u._on_ready = self._unit_ready
+            u.symm_off = off
+            if self.native_comm is not None:
+                off += u.numel
+                u.reduced = torch.empty(u.shard_numel, dtype=torch.float32, device=u.device)
+            self.units.append(u)
         self._last_micro = True
+        self.use_multicast = False       # NVLS multimem.st for the parameter push (opt-in after validation)
         self._norm_buf = None
         self.last_grad_norm: Optional[torch.Tensor] = None
         self._install_hooks()
@@ -219,6 +244,8 @@ class ZeroOptimizer:
     def _reduce_unit(self, u: ParamUnit) -> None:
         st = self.st
         g = u.flat_grad
+        if self.native_comm is not None:
+            return self._reduce_unit_native(u)
         if st.dp == 1:
             u.grad_shard = g
             return
@@ -327,6 +354,9 @@ class ZeroOptimizer:
         st = self.st
         lr = self.lr if lr is None else lr
         self._finish_reductions()
+        PARAM_GENERATION[0] += 1
+        if self.native_comm is not None:
+            return self._step_native(lr)
         self._sync_replicated_grads()
         # losses are already divided by grad_accum_steps by the engine (loss_scale): only 1/dp is left
         inv = 1.0 / st.dp
@@ -351,6 +381,82 @@ class ZeroOptimizer:
                 dist.all_gather_into_tensor(u.flat_param, u.flat_param[u.shard_lo:u.shard_hi].clone()
                                             if dist.get_backend(st.dp_group) == "gloo"
                                             else u.flat_param[u.shard_lo:u.shard_hi], group=st.dp_group)
+        self.zero_grad()
+        return self.last_grad_norm
+
+
+    # ---- native (NVLink peer-memory) gradient / parameter path: K7 ---------------------------------
+    def _init_native_comm(self, named, comm: str):
+        """Symmetric buffers for the fused reduce-scatter + AdamW + all-gather kernels.  Used when: CUDA,
+        dp > 1, ZeRO-1 (persistent buckets), bf16 gradients, no TP/PP sharing of the norm (tp == pp == 1)."""
+        st = self.st
+        if comm == "nccl" or st.dp <= 1 or st.device.type != "cuda" or self.zero_stage != 1:
+            return None
+        if self.grad_dtype != torch.bfloat16 or st.tp != 1 or st.pp != 1:
+            return None
+        from ..ops import functional as ops
+        if ops.kernel_config().optimizer != "native":
+            return None
+        try:
+            from ..comms import symm
+            from ..ops import native
+            if not symm.available() or not native.has_symbol("llmctl_rs_sumsq"):
+                return None
+            total = sum(_unit_numel(m, st.dp) for _, m in named)
+            nc = {"params": symm.SymmBuffer(total, torch.bfloat16, st.dp_group, st.device),
+                  "grads": symm.SymmBuffer(total, torch.bfloat16, st.dp_group, st.device),
+                  "scalars": symm.SymmBuffer(64, torch.float32, st.dp_group, st.device),
+                  "stream": torch.cuda.Stream(device=st.device), "epoch_rs": 0, "epoch_step": 0,
+                  "scratch": torch.empty(148 * 2, dtype=torch.float32, device=st.device),
+                  "norm": torch.zeros(1, dtype=torch.float32, device=st.device), "first_of_step": True}
+            nc["scalars"].tensor.zero_()
+            torch.cuda.synchronize(st.device)
+            nc["params"].barrier()
+            _register_k7_signatures()
+            return nc
+        except Exception as e:  # noqa: BLE001 - symmetric memory unavailable: NCCL path
+            if comm == "native":
+                raise
+            import logging
+            logging.getLogger("llmctl.zero").warning("native comm unavailable (%s: %s); using NCCL", type(e).__name__, e)
+            return None
+
+    def _reduce_unit_native(self, u: ParamUnit) -> None:
+        from ..ops import native
+        nc, st = self.native_comm, self.st
+        main = torch.cuda.current_stream(st.device)
+        ev = torch.cuda.Event()
+        ev.record(main)
+        nc["stream"].wait_event(ev)
+        nc["epoch_rs"] += 1
+        with torch.cuda.stream(nc["stream"]):
+            native.call("llmctl_rs_sumsq", nc["grads"].peers, u.symm_off, nc["grads"].pads, st.dp_rank, st.dp,
+                        u.shard_lo, u.shard_numel, u.reduced.data_ptr(), nc["scratch"].data_ptr(),
+                        nc["scratch"].numel(), nc["scalars"].tensor.data_ptr(), int(not nc["first_of_step"]),
+                        nc["epoch_rs"], nc["stream"].cuda_stream)
+        nc["first_of_step"] = False
+        u.grad_shard = u.reduced
+
+    def _step_native(self, lr: float) -> torch.Tensor:
+        from ..ops import native
+        nc, st = self.native_comm, self.st
+        main = torch.cuda.current_stream(st.device)
+        main.wait_stream(nc["stream"])
+        self.step_count += 1
+        nc["epoch_step"] += 1
+        bc1 = 1.0 - self.betas[0] ** self.step_count
+        bc2 = 1.0 - self.betas[1] ** self.step_count
+        live = [u for u in self.units if u.grad_shard is not None]
+        mc = nc["params"].multicast_ptr if self.use_multicast else 0
+        for i, u in enumerate(live):
+            native.call("llmctl_adam_allgather", nc["params"].peers, u.symm_off, mc or None, nc["params"].pads,
+                        nc["scalars"].peers, st.dp_rank, st.dp, u.shard_lo, u.shard_numel, u.master.data_ptr(),
+                        u.exp_avg.data_ptr(), u.exp_avg_sq.data_ptr(), u.reduced.data_ptr(), lr, self.betas[0],
+                        self.betas[1], self.eps, self.weight_decay, bc1, bc2, 1.0 / st.dp,
+                        float(self.grad_clip or 0.0), nc["norm"].data_ptr(), nc["epoch_step"], int(i == 0),
+                        int(i == len(live) - 1), main.cuda_stream)
+        nc["first_of_step"] = True
+        self.last_grad_norm = nc["norm"]
         self.zero_grad()
         return self.last_grad_norm
 
@@ -416,6 +522,32 @@ class _FullParams:
         for u in self.opt.units:
             u.release_params()
         return False
+
+
+def _unit_numel(module: nn.Module, dp: int) -> int:
+    off = 0
+    for p in module.parameters():
+        if p.requires_grad:
+            off += _round_up(p.numel(), _ALIGN)
+    return _round_up(off, _ALIGN * dp)
+
+
+_k7_registered = False
+
+
+def _register_k7_signatures() -> None:
+    global _k7_registered
+    if _k7_registered:
+        return
+    import ctypes
+    from ..comms.symm import PeerTable
+    from ..ops import native
+    vp, i32, i64, f32, u32 = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_float, ctypes.c_uint
+    native.register_signature("llmctl_rs_sumsq", [PeerTable, i64, PeerTable, i32, i32, i64, i64, vp, vp, i32, vp, i32, u32, vp])
+    native.register_signature("llmctl_adam_allgather",
+                              [PeerTable, i64, vp, PeerTable, PeerTable, i32, i32, i64, i64, vp, vp, vp, vp] + [f32] * 9 +
+                              [vp, u32, i32, i32, vp])
+    _k7_registered = True
 
 
 def default_units(model: nn.Module):

@@ -220,6 +220,13 @@ class TrainingEngine:
         self.model = build_model(cfg, dtype=self.dtype, device=st.device, layer_range=layer_range,
                                  activation_checkpoint=c.activation_checkpoint,
                                  max_seq_len=max(c.seq_len, 1), seed=c.seed)
+        if st.tp > 1 and st.sequence_parallel and st.device.type == "cuda" and c.kernels == "native":
+            # fused all-gather->GEMM / GEMM->reduce-scatter over NVLink peer memory (K1 / K2)
+            try:
+                from ..comms import fused
+                fused.init_tp_workspace(max_tokens=c.batch_size * c.seq_len, hidden=max(cfg.hidden, cfg.ffn // st.tp * 2))
+            except Exception as e:  # noqa: BLE001 - symmetric memory unavailable: NCCL collectives
+                self.logger.warning("fused TP workspace unavailable (%s: %s); using NCCL collectives", type(e).__name__, e)
         from ..serve.tokenizer import load_tokenizer
         self.tokenizer = load_tokenizer(c.model_name_or_path, cfg.vocab_size)
         if self.is_main:

@@ -1,0 +1,236 @@
+"""Multi-GPU worker (one process per GPU, launched by torchrun from tests/test_multigpu.py or by hand):
+numerics of every fused compute+collective kernel against NCCL + PyTorch, and device-timed comparisons."""
+import json
+import os
+import sys
+import tempfile
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT))
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+
+def time_max(fn, iters=10, warm=3):
+    for _ in range(warm):
+        fn()
+    dist.barrier(); torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record(); torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1) / iters], device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t)
+
+
+def case_probe(out):
+    from llmctl_b200.comms import symm
+    buf = symm.SymmBuffer(1 << 20, torch.bfloat16)
+    out["symm"] = {"world": buf.world, "multicast_ptr": hex(buf.multicast_ptr), "signal_pad_bytes": buf.signal_pad_bytes,
+                   "p2p": [torch.cuda.can_device_access_peer(buf.rank, r) for r in range(buf.world) if r != buf.rank]}
+    buf.tensor.fill_(buf.rank + 1)
+    torch.cuda.synchronize(); buf.barrier()
+    peer = (buf.rank + 1) % buf.world
+    t = buf.handle.get_buffer(peer, (16,), torch.bfloat16)
+    out["symm"]["peer_read_ok"] = bool((t == peer + 1).all())
+    buf.barrier()
+
+
+def case_tp_kernels(out, M=4096, K=4096, N=1536, Kl=1376):
+    """K1 ag_gemm, K2 gemm_rs (+ reduce + rmsnorm), K11 — numerics vs NCCL + PyTorch and timings."""
+    from llmctl_b200.comms import fused
+    from llmctl_b200.comms.mesh import init_mesh
+    from llmctl_b200.ops import native
+    st = init_mesh(tp=dist.get_world_size(), sequence_parallel=True)
+    ctx = fused.init_tp_workspace(max_tokens=M, hidden=4096)
+    assert ctx is not None, "fused TP context unavailable"
+    W, r = st.tp, st.tp_rank
+    Ms = M // W
+    torch.manual_seed(100 + r)
+    x_local = torch.randn(Ms, K, device="cuda").bfloat16()
+    w = (0.02 * torch.randn(N, K, device="cuda")).bfloat16()
+    # ---- K1 ----
+    res = {}
+    for it in range(3):                                  # several calls: exercises the alternating buffers / epochs
+        y, xg = ctx.ag_gemm(x_local, w)
+        gathered = torch.empty(M, K, device="cuda", dtype=torch.bfloat16)
+        dist.all_gather_into_tensor(gathered, x_local)
+        ref = gathered.float() @ w.float().t()
+        err = (y.float() - ref).abs().max().item() / ref.abs().max().item()
+        per_chunk = [((y.float() - ref)[c * Ms:(c + 1) * Ms].abs().max() / ref.abs().max()).item() for c in range(W)]
+        assert torch.equal(xg, gathered), f"gathered activation mismatch (call {it})"
+        assert err < 2e-2, f"ag_gemm rel err {err} on call {it}, per source chunk {per_chunk}"
+    res["ag_gemm_rel_err"] = err
+
+    def base_ag():
+        g = torch.empty(M, K, device="cuda", dtype=torch.bfloat16)
+        dist.all_gather_into_tensor(g, x_local)
+        return g @ w.t()
+    res["ag_gemm_ms"] = time_max(lambda: ctx.ag_gemm(x_local, w))
+    res["nccl_ag_then_cublas_ms"] = time_max(base_ag)
+    res["gemm_only_cublas_ms"] = time_max(lambda: gathered @ w.t())
+    # ---- K2 ----
+    torch.manual_seed(200 + r)
+    x2 = torch.randn(M, Kl, device="cuda").bfloat16()
+    w2 = (0.02 * torch.randn(4096, Kl, device="cuda")).bfloat16()
+    resid = torch.randn(Ms, 4096, device="cuda").bfloat16()
+    nw = (1 + 0.1 * torch.randn(4096, device="cuda")).bfloat16()
+    for it in range(3):
+        h, y2, rstd = ctx.gemm_rs(x2, w2, residual=resid, norm_w=nw)
+        part = (x2.float() @ w2.float().t()).bfloat16()        # each rank's partial is rounded to bf16 before the sum
+        full = part.float().clone()
+        dist.all_reduce(full)
+        href = (full[r * Ms:(r + 1) * Ms] + resid.float())
+        e1 = (h.float() - href).abs().max().item() / href.abs().max().item()
+        hq = h.float()
+        yref = hq * torch.rsqrt(hq.pow(2).mean(-1, keepdim=True) + 1e-5) * nw.float()
+        e2 = (y2.float() - yref).abs().max().item()
+        assert e1 < 2e-2 and e2 < 5e-2, f"gemm_rs errs {e1} {e2} on call {it}"
+    res["gemm_rs_rel_err"] = e1
+
+    def base_rs():
+        p = x2 @ w2.t()
+        o = torch.empty(Ms, 4096, device="cuda", dtype=torch.bfloat16)
+        dist.reduce_scatter_tensor(o, p)
+        hh = o + resid
+        return torch.nn.functional.rms_norm(hh, (4096,), nw, 1e-5)
+    res["gemm_rs_norm_ms"] = time_max(lambda: ctx.gemm_rs(x2, w2, residual=resid, norm_w=nw))
+    res["cublas_nccl_rs_norm_ms"] = time_max(base_rs)
+    res["gemm_only_cublas_ms_k2"] = time_max(lambda: x2 @ w2.t())
+    # ---- K11 ----
+    B, H = 8, 4096
+    sb = ctx.stage[0]
+    for it in range(1, 4):
+        part = torch.randn(B, H, device="cuda").bfloat16()
+        sb.tensor[:B * H].view(B, H).copy_(part)
+        res_in = torch.randn(B, H, device="cuda").bfloat16()
+        hout, yout = torch.empty_like(res_in), torch.empty_like(res_in)
+        native.call("llmctl_ar_residual_rmsnorm", sb.peers, 0, None, sb.pads, 16, r, W, res_in.data_ptr(), hout.data_ptr(),
+                    nw.data_ptr(), yout.data_ptr(), B, H, 1e-5, it, native.stream_ptr())
+        tot = part.float().clone(); dist.all_reduce(tot)
+        hr = (tot + res_in.float())
+        assert (hout.float() - hr).abs().max().item() < 0.1, "K11 h mismatch"
+        hq = hout.float()
+        yr = hq * torch.rsqrt(hq.pow(2).mean(-1, keepdim=True) + 1e-5) * nw.float()
+        assert (yout.float() - yr).abs().max().item() < 5e-2, "K11 y mismatch"
+        torch.cuda.synchronize(); dist.barrier()
+    ep = [10]
+
+    def k11():
+        ep[0] += 1
+        native.call("llmctl_ar_residual_rmsnorm", sb.peers, 0, None, sb.pads, 16, r, W, res_in.data_ptr(), hout.data_ptr(),
+                    nw.data_ptr(), yout.data_ptr(), B, H, 1e-5, ep[0], native.stream_ptr())
+
+    def base_k11():
+        t = part.clone(); dist.all_reduce(t)
+        return torch.nn.functional.rms_norm(t + res_in, (H,), nw, 1e-5)
+    res["ar_rmsnorm_us"] = 1e3 * time_max(k11, iters=50)
+    res["nccl_ar_add_norm_us"] = 1e3 * time_max(base_k11, iters=50)
+    if sb.multicast_ptr:
+        def k11mc():
+            ep[0] += 1
+            native.call("llmctl_ar_residual_rmsnorm", sb.peers, 0, sb.multicast_ptr, sb.pads, 16, r, W, res_in.data_ptr(),
+                        hout.data_ptr(), nw.data_ptr(), yout.data_ptr(), B, H, 1e-5, ep[0], native.stream_ptr())
+        k11mc(); torch.cuda.synchronize()
+        assert (hout.float() - hr).abs().max().item() < 0.1, "K11 multimem mismatch"
+        res["ar_rmsnorm_multimem_us"] = 1e3 * time_max(k11mc, iters=50)
+    out["tp_kernels"] = res
+    fused.shutdown()
+
+
+def _engine(kw, model=None):
+    from llmctl_b200.comms import mesh
+    from llmctl_b200.models.config import ModelConfig
+    from llmctl_b200.runtime.engine import TrainingEngine, create_training_config
+    cfg = model or ModelConfig(name="mg", layers=2, hidden=1024, ffn=2816, heads=8, vocab_size=8192, max_position_embeddings=512)
+    base = dict(model_name_or_path="gpt-125m", output_dir=tempfile.mkdtemp(), batch_size=2, seq_len=256, max_steps=4,
+                logging_steps=1, eval_steps=0, save_steps=0, learning_rate=1e-3, log_level="warning", metrics_jsonl=False, seed=11)
+    base.update(kw)
+    eng = TrainingEngine(create_training_config(**base))
+    eng.config.model_name_or_path = cfg
+    eng.load_model_and_tokenizer(); eng.prepare_datasets()
+    return eng
+
+
+def case_zero_native(out):
+    """K7: fused reduce-scatter + AdamW + all-gather vs the NCCL path, same init, 4 steps."""
+    from llmctl_b200.parallel.zero import ZeroOptimizer
+    traj = {}
+    for comm in ("nccl", "native"):
+        eng = _engine(dict(zero_stage=1))
+        c = eng.config
+        eng.optimizer = ZeroOptimizer(eng.model, lr=c.learning_rate, betas=tuple(c.betas), eps=c.adam_eps, weight_decay=c.weight_decay,
+                                      zero_stage=1, grad_clip=c.gradient_clipping, state=eng.state, comm=comm)
+        from llmctl_b200.runtime.engine import LRSchedule
+        eng.scheduler = LRSchedule(c.learning_rate, 0, 100, "constant")
+        if comm == "native":
+            assert eng.optimizer.native_comm is not None, "native comm path was not enabled"
+        losses = []
+        for _ in range(4):
+            o = eng.train_step()
+            losses.append((eng._reduce_scalar(o["loss"]), float(o["grad_norm"])))
+        traj[comm] = losses
+        p0 = torch.cat([p.detach().float().reshape(-1)[:1000] for p in eng.model.parameters()])
+        traj[comm + "_p"] = p0
+        from llmctl_b200.comms import mesh
+        torch.cuda.synchronize(); dist.barrier()
+        mesh.reset_state()
+    for (la, ga), (lb, gb) in zip(traj["nccl"], traj["native"]):
+        assert abs(la - lb) < 2e-2 * max(1, abs(la)), f"loss nccl {traj['nccl']} native {traj['native']}"
+        assert abs(ga - gb) < 5e-2 * max(1, abs(ga)), f"gnorm nccl {traj['nccl']} native {traj['native']}"
+    dp = (traj["nccl_p"] - traj["native_p"]).abs().max().item()
+    assert dp < 5e-2, f"params diverged: {dp}"
+    out["zero_native"] = {"nccl": traj["nccl"], "native": traj["native"], "max_param_diff": dp}
+
+
+def case_tp_sp_engine(out):
+    """TP=world + SP training with the fused K1/K2 linears vs the NCCL collectives."""
+    from llmctl_b200.comms import fused, mesh
+    res = {}
+    for mode in ("nccl", "fused"):
+        eng = _engine(dict(tensor_parallel=dist.get_world_size(), sequence_parallel=True))
+        if mode == "fused":
+            assert fused.init_tp_workspace(max_tokens=2 * 256, hidden=1024) is not None
+        else:
+            fused.shutdown()
+        eng.setup_optimizer_and_scheduler()
+        res[mode] = [eng._reduce_scalar(eng.train_step()["loss"]) for _ in range(4)]
+        torch.cuda.synchronize(); dist.barrier()
+        fused.shutdown(); mesh.reset_state()
+    for a, b in zip(res["nccl"], res["fused"]):
+        assert abs(a - b) < 3e-2 * max(1, abs(a)), f"{res}"
+    out["tp_sp_engine"] = res
+
+
+CASES = {"probe": case_probe, "tp_kernels": case_tp_kernels, "zero_native": case_zero_native, "tp_sp_engine": case_tp_sp_engine}
+
+
+def main():
+    names = sys.argv[1:] or list(CASES)
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    out = {}
+    failed = []
+    for n in names:
+        try:
+            CASES[n](out)
+        except Exception as e:  # noqa: BLE001
+            import traceback
+            failed.append(n)
+            out[n + "_error"] = f"{type(e).__name__}: {e}"
+            if dist.get_rank() == 0:
+                traceback.print_exc()
+            break     # ranks may now be out of step: stop here
+    if dist.get_rank() == 0:
+        print("MGPU_RESULT " + json.dumps(out, default=str))
+    dist.destroy_process_group()
+    sys.exit(1 if failed else 0)
+
+
+if __name__ == "__main__":
+    main()

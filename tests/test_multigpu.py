@@ -1,0 +1,43 @@
+"""Fused compute+collective kernels on >= 2 GPUs (skipped on a single-GPU box)."""
+import json
+import os
+import subprocess
+import sys
+from pathlib import Path
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = Path(__file__).resolve().parent.parent
+
+
+def _run(cases, n=2, timeout=600):
+    if not torch.cuda.is_available() or torch.cuda.device_count() < n:
+        pytest.skip(f"needs {n} GPUs")
+    from dist_utils import free_port
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}", "--master-addr", "127.0.0.1",
+           "--master-port", str(free_port()), str(ROOT / "tests" / "mgpu_worker.py")] + cases
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, env=dict(os.environ, PYTHONPATH=str(ROOT)))
+    line = [l for l in r.stdout.splitlines() if l.startswith("MGPU_RESULT ")]
+    assert r.returncode == 0 and line, r.stdout[-3000:] + r.stderr[-3000:]
+    return json.loads(line[-1][len("MGPU_RESULT "):])
+
+
+def test_symmetric_memory_probe(cuda_device):
+    out = _run(["probe"])
+    assert out["symm"]["peer_read_ok"]
+
+
+def test_fused_tp_kernels(cuda_device):
+    out = _run(["tp_kernels"])
+    assert out["tp_kernels"]["ag_gemm_rel_err"] < 2e-2 and out["tp_kernels"]["gemm_rs_rel_err"] < 2e-2
+
+
+def test_zero_native_matches_nccl(cuda_device):
+    out = _run(["zero_native"])
+    assert out["zero_native"]["max_param_diff"] < 5e-2
+
+
+def test_tp_sp_engine_fused_matches_nccl(cuda_device):
+    _run(["tp_sp_engine"])

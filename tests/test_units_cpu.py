@@ -1,0 +1,201 @@
+"""Unit tests the reference never had: planner, config schemas, health thresholds, autotuner,
+plugin registry, checkpoint GC, LR schedule, export re-sharding, roofline."""
+import json
+import math
+import time
+
+import pytest
+import torch
+
+
+def test_planner_param_count_and_measured_search():
+    from llmctl_b200.models.config import get_preset
+    from llmctl_b200.partition.planner import HardwareNumbers, MeasuredCostModel, ReferenceCostModel
+    m7 = get_preset("gpt-7b")
+    assert m7.num_parameters() == 6_738_415_616                      # reference configs/models/llama-7b.json:23
+    ref = ReferenceCostModel(m7.to_dict(), {"gpu": {"count": 8}})
+    assert ref.parameters() == 5_164_761_088                         # the reference's (defective) estimate, golden
+    assert abs(ref.model_memory_gb() - 57.72) < 0.01
+    assert ref.manual(2, 1, 0).zero_stage == 0                       # explicit 0 stays 0 (D9)
+    hw = HardwareNumbers(gpus=8)
+    plans = MeasuredCostModel(m7, hw, seq_len=2048).search(global_batch=64)
+    assert plans and plans[0].estimated_memory_gb <= 0.92 * 180
+    assert all(p.tensor_parallel * p.pipeline_parallel * p.data_parallel == 8 for p in plans)
+    assert plans == sorted(plans, key=lambda p: -p.estimated_tokens_per_s)
+    m13 = get_preset("gpt-13b")
+    pinned = MeasuredCostModel(m13, hw, 4096).search(global_batch=32, pins={"tensor_parallel": 4, "pipeline_parallel": 2})
+    assert pinned and all((p.tensor_parallel, p.pipeline_parallel) == (4, 2) for p in pinned)
+    assert pinned[0].breakdown["pp_bubble"] > 0
+    small = MeasuredCostModel(m13, HardwareNumbers(gpus=8, memory_gb=24), 4096).search(global_batch=32)
+    assert all(p.estimated_memory_gb <= 0.92 * 24 for p in small)    # memory cap is honoured
+
+
+def test_partition_layers():
+    from llmctl_b200.parallel.pp import partition_layers
+    assert partition_layers(32, 4) == [(0, 8), (8, 16), (16, 24), (24, 32)]
+    r = partition_layers(40, 3)
+    assert r[0][0] == 0 and r[-1][1] == 40 and all(a < b for a, b in r) and all(r[i][1] == r[i + 1][0] for i in range(2))
+    with pytest.raises(ValueError):
+        partition_layers(2, 4)
+
+
+def test_config_schemas_and_precedence(tmp_path):
+    import tomli_w
+    from llmctl_b200.cli.commands.init import default_training_config
+    from llmctl_b200.config.schemas import (ModelSchema, ServeConfig, load_training_preset, resolve_training_config)
+    with pytest.raises(Exception):
+        ModelSchema.model_validate({"name": "x", "layers": 0, "hidden": 8, "heads": 2, "vocab_size": 10})
+    with pytest.raises(Exception):
+        ServeConfig(artifact="a", scheduler="bogus")
+    preset = tmp_path / "configs" / "default.toml"
+    preset.parent.mkdir(parents=True)
+    preset.write_text(tomli_w.dumps(default_training_config("gpt", "125m", "proj")))
+    ps = load_training_preset(preset)
+    assert ps.checkpoint.async_ is True and ps.parallel.activation_checkpoint == "selective"
+    plan = tmp_path / "plan.toml"
+    plan.write_text(tomli_w.dumps({"parallelism": {"tensor_parallel": 2, "pipeline_parallel": 1, "data_parallel": 4, "zero_stage": 3,
+                                                   "micro_batch_size": 2, "global_batch_size": 32, "sequence_parallel": True}}))
+    cfg = resolve_training_config(preset, plan, {"learning_rate": 1e-5, "zero_stage": None})
+    assert cfg["tensor_parallel"] == 2 and cfg["zero_stage"] == 3 and cfg["sequence_parallel"] is True   # plan > preset
+    assert cfg["gradient_accumulation_steps"] == 4 and cfg["batch_size"] == 2
+    assert cfg["learning_rate"] == 1e-5                                                                  # CLI > files
+    assert cfg["weight_decay"] == 0.1 and cfg["scheduler"] == "cosine"                                   # preset > defaults
+
+
+def test_health_thresholds_fire():
+    from llmctl_b200.metrics.health import (HealthStatus, InferenceHealthMonitor, SystemHealthMonitor, TrainingHealthMonitor)
+
+    class Fake(SystemHealthMonitor):
+        def __init__(self, m):
+            super().__init__()
+            self._m = m
+
+        def collect(self):
+            return self._m
+    r = Fake({"cpu_usage": 10, "memory_usage": 10, "disk_space": 90, "gpu_memory": 10}).get_health_report()
+    assert r.status == HealthStatus.WARNING and r.checks["disk_space"] is False      # D12: disk threshold fires
+    r = Fake({"cpu_usage": 10, "memory_usage": 10, "disk_space": 10, "gpu_memory": 99}).get_health_report()
+    assert r.status == HealthStatus.CRITICAL and r.checks["gpu_memory"] is False      # D12: GPU-memory threshold fires
+    t = TrainingHealthMonitor(stall_seconds=0.05)
+    assert t.get_health_report().status == HealthStatus.UNKNOWN
+    t.update_metrics(1, 2.5, 1.0)
+    assert t.get_health_report().status == HealthStatus.HEALTHY
+    t.update_metrics(2, float("nan"), 1.0)
+    assert t.get_health_report().status == HealthStatus.CRITICAL
+    t.update_metrics(3, 2.0, 500.0)
+    assert t.get_health_report().status == HealthStatus.WARNING
+    t.update_metrics(4, 2.0, 1.0); time.sleep(0.1)
+    assert t.get_health_report().status == HealthStatus.CRITICAL                      # stalled
+    i = InferenceHealthMonitor()
+    for k in range(20):
+        i.record_request(0.1, success=k != 0)
+    assert i.get_health_report().status == HealthStatus.CRITICAL                      # 5 % errors
+    i2 = InferenceHealthMonitor(); i2.record_request(11.0); i2.update_queue(5)
+    assert i2.get_health_report().status == HealthStatus.WARNING
+
+
+def test_observability_feeds_prometheus():
+    from prometheus_client import CollectorRegistry, generate_latest
+    from llmctl_b200.metrics.observability import ObservabilityManager
+    om = ObservabilityManager()
+    reg = CollectorRegistry()
+    om.enable_prometheus(port=None, registry=reg)
+    om.record_training_step(step=3, loss=2.0, learning_rate=1e-4, tokens_per_second=1000.0, grad_norm=0.5, step_time=0.1, mfu=0.4)
+    om.record_inference_request(latency=0.2, tokens=10, ttft=0.05)
+    text = generate_latest(reg).decode()
+    assert "llmctl_training_loss 2.0" in text and "llmctl_training_steps_total 3.0" in text   # D15: counters move
+    assert 'llmctl_inference_requests_total{status="ok"} 1.0' in text and "llmctl_inference_latency_seconds_count 1.0" in text
+
+
+def test_autotuner_grid_search_and_cache(tmp_path):
+    from llmctl_b200.plugins.autotuning import AutoTuner, Tunable, TuningConfig
+
+    class Toy(Tunable):
+        calls = 0
+
+        def get_parameter_space(self):
+            return {"a": [1, 2, 3, 4], "b": [10, 20]}
+
+        def validate_parameters(self, p):
+            return p["a"] != 4
+
+        def set_parameters(self, p):
+            self.p = p
+
+        def benchmark(self, x):
+            Toy.calls += 1
+            return abs(self.p["a"] - 2) + self.p["b"] / 100.0
+    t = AutoTuner(TuningConfig(max_iterations=50))
+    r = t.grid_search(Toy(), None, "toy")
+    assert r.best_config == {"a": 2, "b": 10} and r.iterations == 6 and r.improvement > 0
+    n = Toy.calls
+    assert t.grid_search(Toy(), None, "toy") is r and Toy.calls == n                  # cache hit
+    t.save_results(str(tmp_path / "c.json"))
+    t2 = AutoTuner(); t2.load_results(str(tmp_path / "c.json"))
+    assert t2.results_cache["toy"].best_config == {"a": 2, "b": 10}
+    assert AutoTuner(TuningConfig(max_iterations=2)).grid_search(Toy(), None).iterations == 2   # max_iterations honoured (D13)
+
+
+def test_plugin_registry(tmp_path, monkeypatch):
+    from llmctl_b200.plugins.registry import PluginRegistry
+    (tmp_path / "my_plugin.py").write_text("class S:\n    def schedule(self, reqs):\n        return reqs[:1]\n\ndef register():\n    return {'first-only': S}\n")
+    monkeypatch.syspath_prepend(str(tmp_path))
+    monkeypatch.setenv("LLMCTL_PLUGINS", "schedulers:my_plugin")
+    reg = PluginRegistry()
+    assert reg.get("schedulers", "first-only")().schedule([1, 2]) == [1]
+    assert {"dynamic", "simple", "vllm-like"} <= set(reg.list("schedulers")) and "rmsnorm" in reg.list("kernels")
+    with pytest.raises(KeyError):
+        reg.register("bogus", "x", object())
+
+
+def test_lr_schedule_and_config_validation():
+    from llmctl_b200.runtime.engine import LRSchedule, create_training_config
+    s = LRSchedule(1.0, warmup=4, total=14, kind="linear")
+    assert [round(s.lr_at(i), 3) for i in (0, 3, 4, 9, 14)] == [0.25, 1.0, 1.0, 0.5, 0.0]
+    c = LRSchedule(1.0, 0, 10, "cosine")
+    assert abs(c.lr_at(5) - 0.5) < 1e-6
+    with pytest.raises(TypeError):
+        create_training_config(not_a_field=1)
+
+
+def test_checkpoint_gc_and_latest(tmp_path):
+    from llmctl_b200.io.checkpoint import gc_checkpoints, latest_checkpoint, list_checkpoints
+    for step, complete in ((10, True), (20, True), (30, False), (40, True)):
+        d = tmp_path / f"checkpoint-{step}"; d.mkdir()
+        if complete:
+            (d / "COMPLETE").write_text(str(step))
+    assert [d.name for d in list_checkpoints(tmp_path)] == ["checkpoint-10", "checkpoint-20", "checkpoint-40"]
+    assert latest_checkpoint(tmp_path).name == "checkpoint-40"
+    removed = {d.name for d in gc_checkpoints(tmp_path, keep_latest=2)}
+    assert removed == {"checkpoint-10", "checkpoint-30"}                               # oldest complete + stale incomplete
+    assert sorted(p.name for p in tmp_path.iterdir()) == ["checkpoint-20", "checkpoint-40"]
+
+
+def test_tp_merge_split_roundtrip():
+    from llmctl_b200.io.export import merge_tp, split_tp, to_hf_llama
+    full = torch.arange(24 * 4, dtype=torch.float32).view(24, 4)
+    for packed, dim in ((3, 0), (1, 0), (1, 1), (2, 0)):
+        shards = [split_tp(full, dim, packed, 2, r) for r in range(2)]
+        assert torch.equal(merge_tp(shards, dim, packed), full)
+    hf = to_hf_llama({"blocks.0.attn.qkv.weight": full, "blocks.0.mlp.up.weight": full, "embed.weight": full})
+    assert hf["model.layers.0.self_attn.k_proj.weight"].shape == (8, 4) and "model.embed_tokens.weight" in hf
+
+
+def test_roofline_report():
+    from llmctl_b200.metrics.roofline import RooflinePoint, peak_flops
+    r = RooflinePoint("gemm", seconds=2 * 8192 ** 3 / peak_flops(False) * 2, flops=2 * 8192 ** 3).report()
+    assert r["bound"] == "compute" and abs(r["fraction_of_roofline"] - 0.5) < 1e-6
+    assert RooflinePoint("copy", 1.0, hbm_bytes=1e12, nvlink_bytes=1e12).report()["bound"] == "nvlink"
+
+
+def test_dataset_determinism_and_resume():
+    from llmctl_b200.io.dataset import SyntheticTokenDataset, TokenLoader
+    ds = SyntheticTokenDataset(1000, 16, seed=3)
+    assert (ds[5] == SyntheticTokenDataset(1000, 16, seed=3)[5]).all() and (ds[5] != ds[6]).any()
+    a = TokenLoader(ds, 2, dp_rank=0, dp_size=2); b = TokenLoader(ds, 2, dp_rank=1, dp_size=2)
+    ta, _ = a.next_batch(); tb, _ = b.next_batch()
+    assert not torch.equal(ta, tb)                                                     # ranks see disjoint samples
+    a.next_batch(); st = a.state_dict()
+    nxt, _ = a.next_batch()
+    c = TokenLoader(ds, 2, dp_rank=0, dp_size=2); c.load_state_dict(st)
+    assert torch.equal(c.next_batch()[0], nxt)                                         # resumable cursor
