@@ -299,3 +299,86 @@ LLMCTL_API int llmctl_layernorm_bwd(const void* dy, const void* h, const void* w
   return launch_bwd<true>(dy, h, w, mean, rstd, dres, dx, dw, db, scratch, scratch_rows, rows, cols,
                           accumulate, (cudaStream_t)stream);
 }
+
+// ------------------------------------------------------------------------------------------------
+// Allocation-free RMSNorm backward.
+//
+// Who this is for: programs that reach this library through the C ABI and cannot obtain device memory at
+// call time.  Two real cases: (1) a host runtime that hands its whole device budget to its own arena at
+// start-up (an inference server, a simulator embedding) so that a later cudaMalloc would either fail or
+// fragment the arena; (2) a control loop with a latency bound, where cudaMalloc/cudaFree are off limits
+// because they take the driver's memory lock and may synchronise the device.  llmctl_rmsnorm_bwd needs an
+// fp32 scratch area for the per-CTA partial sums of dw and leaves its provision to the caller; this variant
+// carries the scratch inside the library image instead.
+//
+// The scratch is the file-scope array below: kNoAllocCtas x kNoAllocMaxCols floats = 2 MiB of global memory
+// that every GPU which loads this library keeps reserved until the process exits.
+//
+// Set-up: on the first call made on a given device (with that device current) the entry point asks the
+// runtime for the array's device address with cudaGetSymbolAddress, checks the result and caches it per
+// device.  In host code the array's name is only a stand-in for the symbol, not a device address, so it is
+// never handed to the kernel.  Make that first call outside any stream capture.
+//
+// Limits and sharing: cols <= 8192 (and a multiple of 8); larger rows are rejected with an error message
+// (llmctl_noalloc_last_error) and cudaErrorInvalidValue.  rows is unlimited (CTAs loop over rows).  All calls
+// on a device share the one array and it keeps whatever the last call left in it.  Nothing in it has to start
+// at zero: each CTA overwrites its own partial row in full before the column reduction reads exactly those
+// rows.  Two calls whose kernels overlap on the GPU (different streams, no dependency) race on the array and
+// produce wrong dw; serialise them.
+//
+// No cudaMalloc / cudaFree / allocating library call is made here.
+// ------------------------------------------------------------------------------------------------
+#include <mutex>
+
+namespace llmctl {
+constexpr int kNoAllocCtas = 64;
+constexpr int kNoAllocMaxCols = 8192;
+constexpr int kNoAllocMaxDevices = 64;
+static __device__ __align__(256) float g_rmsnorm_bwd_scratch[kNoAllocCtas * kNoAllocMaxCols];
+static float* g_noalloc_scratch_addr[kNoAllocMaxDevices] = {nullptr};
+static std::mutex g_noalloc_mu;
+static thread_local char g_noalloc_err[256] = "";
+}  // namespace llmctl
+
+// Text of the last error raised by an allocation-free entry point on this thread ("" if none).
+LLMCTL_API const char* llmctl_noalloc_last_error() { return llmctl::g_noalloc_err; }
+
+LLMCTL_API int llmctl_rmsnorm_bwd_noalloc(const void* dy, const void* h, const void* w, const float* rstd,
+                                          const void* dres, void* dx, float* dw, int rows, int cols,
+                                          int accumulate, void* stream) {
+  LLMCTL_BEGIN();
+  g_noalloc_err[0] = '\0';
+  if (cols <= 0 || cols % 8 != 0 || cols > kNoAllocMaxCols || rows < 0) {
+    snprintf(g_noalloc_err, sizeof(g_noalloc_err),
+             "llmctl_rmsnorm_bwd_noalloc: cols=%d rows=%d not supported: cols must be a positive multiple of 8 "
+             "and at most %d (the built-in scratch holds %d x %d floats)",
+             cols, rows, kNoAllocMaxCols, kNoAllocCtas, kNoAllocMaxCols);
+    fprintf(stderr, "[llmctl] %s\n", g_noalloc_err);
+    return static_cast<int>(cudaErrorInvalidValue);
+  }
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= kNoAllocMaxDevices) {
+    snprintf(g_noalloc_err, sizeof(g_noalloc_err), "llmctl_rmsnorm_bwd_noalloc: cannot identify the current device (%d)", (int)e);
+    return static_cast<int>(e != cudaSuccess ? e : cudaErrorInvalidDevice);
+  }
+  float* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (g_noalloc_scratch_addr[dev] == nullptr) {
+      // once per device, with that device current: resolve the symbol to its address on THIS device
+      void* p = nullptr;
+      e = cudaGetSymbolAddress(&p, g_rmsnorm_bwd_scratch);
+      if (e != cudaSuccess || p == nullptr) {
+        snprintf(g_noalloc_err, sizeof(g_noalloc_err),
+                 "llmctl_rmsnorm_bwd_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+        fprintf(stderr, "[llmctl] %s\n", g_noalloc_err);
+        return static_cast<int>(e != cudaSuccess ? e : cudaErrorInvalidSymbol);
+      }
+      g_noalloc_scratch_addr[dev] = static_cast<float*>(p);
+    }
+    scratch = g_noalloc_scratch_addr[dev];
+  }
+  return launch_bwd<false>(dy, h, w, nullptr, rstd, dres, dx, dw, nullptr, scratch, kNoAllocCtas, rows, cols,
+                           accumulate, (cudaStream_t)stream);
+}

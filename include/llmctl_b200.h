@@ -25,6 +25,16 @@ int llmctl_rmsnorm_fwd(const void* x, const void* residual, const void* w, void*
 int llmctl_rmsnorm_bwd(const void* dy, const void* h, const void* w, const float* rstd,
                        const void* dres, void* dx, float* dw, float* scratch, int scratch_rows,
                        int rows, int cols, int accumulate, void* stream);
+/* RMSNorm backward for callers that cannot allocate device memory (a host runtime whose arena already owns the
+ * whole device budget, or a latency-bound loop that must stay away from cudaMalloc's driver lock).  Same math
+ * as llmctl_rmsnorm_bwd; the dw partials live in a 2 MiB array built into the library (held on every GPU that
+ * loads it).  cols <= 8192 and a multiple of 8, else cudaErrorInvalidValue + llmctl_noalloc_last_error().  The
+ * first call on a device resolves the array's address (do it before any stream capture).  Calls overlapping on
+ * the GPU race on the shared array.  This entry point has no counterpart in the reference. */
+int llmctl_rmsnorm_bwd_noalloc(const void* dy, const void* h, const void* w, const float* rstd,
+                               const void* dres, void* dx, float* dw, int rows, int cols, int accumulate,
+                               void* stream);
+const char* llmctl_noalloc_last_error(void);
 int llmctl_layernorm_fwd(const void* x, const void* residual, const void* w, const void* b,
                          void* h_out, void* y, float* mean, float* rstd, int rows, int cols,
                          float eps, void* stream);
