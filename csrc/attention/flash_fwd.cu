@@ -1,0 +1,286 @@
+// K6 (forward): causal flash attention on the 5th-generation tensor cores, head_dim = 128, bf16.
+//
+// One CTA = one (batch, head, 128-query block).  Warp roles:
+//   warp 0     TMA producer  — Q once, then K and V tiles of 128 keys into 2-deep smem rings (3-D tensor maps
+//                              over the packed [tokens, heads, 128] activations, 128-byte swizzle)
+//   warp 1     MMA issuer    — S = Q K^T  (UMMA 128x128x16, both operands K-major, accumulator S[j%2] in TMEM)
+//                              O += P V   (UMMA 128x128x16, A = P from smem (K-major), B = V (MN-major), O in TMEM)
+//   warps 2-5  softmax       — thread = query row: tcgen05.ld S, scale / causal mask / running max, exp2,
+//                              P -> bf16 -> swizzled smem, lazy O rescale in TMEM, final normalisation + store
+// S is double buffered in TMEM so Q K^T of block j+1 runs on the tensor core while the softmax warps work on
+// block j.  The running max is only advanced when it grows by more than 8 (log2 units): between rescales the
+// reference stays put and P may reach 2^8, which fp32 accumulation and bf16 P hold exactly as well — this
+// removes almost all TMEM read-modify-write passes over O.
+// Outputs: O [B,S,H,128] bf16 and the row log-sum-exp (natural log, scale included) for the backward pass.
+//
+// Reference: HF modules choose SDPA/eager attention behind `self.model(**batch)` (reference
+// llmctl/runtime/engine.py:284); the reference's tuner times a naive softmax(QK^T)V (reference
+// llmctl/plugins/autotuning.py:149-188).  Baseline to beat: cuDNN / flash-attn SDPA.
+#include "../common/ptx.cuh"
+#include "../common/tma_host.h"
+#include "../common/util.cuh"
+
+namespace llmctl {
+using namespace ptx;
+
+constexpr int kAD = 128;                 // head dim
+constexpr int kABM = 128;                // queries per CTA
+constexpr int kABN = 128;                // keys per tile
+constexpr int kPanel = 128 * 128;        // bytes of one [128 rows x 64 bf16] swizzled panel
+constexpr int kTile = 2 * kPanel;        // 128 x 128 bf16
+constexpr int kAttnSmem = kTile /*Q*/ + 2 * kTile /*K*/ + 2 * kTile /*V*/ + kTile /*P*/ + 1024;
+constexpr int kAttnThreads = 192;
+constexpr float kRescaleThreshold = 8.f;
+
+__global__ void __launch_bounds__(kAttnThreads, 1)
+flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                 const __grid_constant__ CUtensorMap tmV, __nv_bfloat16* __restrict__ O, long long o_tok_stride,
+                 float* __restrict__ lse, int S, int H, float scale_log2, float scale, int causal) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint64_t bar_q, bar_kfull[2], bar_vfull[2], bar_kempty[2], bar_vempty[2];
+  __shared__ uint64_t bar_sfull[2], bar_sfree[2], bar_pready, bar_pvdone;
+  __shared__ uint32_t tmem_base_smem;
+
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem = smem_raw + (smem_base - smem_u32(smem_raw));
+  uint8_t* sQ = smem;
+  uint8_t* sK = smem + kTile;
+  uint8_t* sV = smem + 3 * kTile;
+  uint8_t* sP = smem + 5 * kTile;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int qblk = gridDim.x - 1 - blockIdx.x;          // heavy (late) query blocks first
+  const int head = blockIdx.y, b = blockIdx.z;
+  const int q0 = qblk * kABM;
+  const int nblk = causal ? (qblk + 1) : (S / kABN);
+  const int tok0 = b * S;
+
+  if (threadIdx.x == 0) {
+    mbar_init(&bar_q, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&bar_kfull[i], 1);
+      mbar_init(&bar_vfull[i], 1);
+      mbar_init(&bar_kempty[i], 1);
+      mbar_init(&bar_vempty[i], 1);
+      mbar_init(&bar_sfull[i], 1);
+      mbar_init(&bar_sfree[i], 4);
+    }
+    mbar_init(&bar_pready, 4);
+    mbar_init(&bar_pvdone, 1);
+    fence_mbar_init();
+  }
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmQ);
+    prefetch_tmap(&tmK);
+    prefetch_tmap(&tmV);
+  }
+  if (warp == 1) tmem_alloc<1>(&tmem_base_smem, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_smem;
+  const uint32_t tS0 = tmem_base, tO = tmem_base + 256;   // S[0] cols 0..127, S[1] 128..255, O 256..383
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_expect_tx(&bar_q, kTile);
+      tma_load_3d(sQ, &tmQ, &bar_q, 0, head, tok0 + q0);
+      tma_load_3d(sQ + kPanel, &tmQ, &bar_q, 64, head, tok0 + q0);
+      for (int j = 0; j < nblk; ++j) {
+        const int st = j & 1;
+        const uint32_t ph = (j >> 1) & 1u;
+        mbar_wait(&bar_kempty[st], ph ^ 1u);
+        mbar_expect_tx(&bar_kfull[st], kTile);
+        tma_load_3d(sK + st * kTile, &tmK, &bar_kfull[st], 0, head, tok0 + j * kABN);
+        tma_load_3d(sK + st * kTile + kPanel, &tmK, &bar_kfull[st], 64, head, tok0 + j * kABN);
+        mbar_wait(&bar_vempty[st], ph ^ 1u);
+        mbar_expect_tx(&bar_vfull[st], kTile);
+        tma_load_3d(sV + st * kTile, &tmV, &bar_vfull[st], 0, head, tok0 + j * kABN);
+        tma_load_3d(sV + st * kTile + kPanel, &tmV, &bar_vfull[st], 64, head, tok0 + j * kABN);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc_qk = make_idesc_bf16(kABM, kABN, 0u, 0u);   // A, B K-major
+      constexpr uint32_t idesc_pv = make_idesc_bf16(kABM, kAD, 0u, 1u);    // A K-major (P), B MN-major (V)
+      const uint32_t q_addr = smem_base;
+      const uint32_t p_addr = smem_base + 5 * kTile;
+      auto issue_qk = [&](int j) {
+        const int st = j & 1;
+        mbar_wait(&bar_kfull[st], (j >> 1) & 1u);
+        mbar_wait(&bar_sfree[st], ((j >> 1) & 1u) ^ 1u);      // softmax finished reading S[st] of block j-2
+        tc_fence_after();
+        const uint32_t k_addr = smem_base + kTile + st * kTile;
+#pragma unroll
+        for (int ks = 0; ks < kAD / 16; ++ks) {
+          const uint32_t off = (ks >> 2) * kPanel + (ks & 3) * 32;
+          umma_ss<1>(tS0 + st * 128, make_smem_desc(q_addr + off, 16, 1024, 2),
+                     make_smem_desc(k_addr + off, 16, 1024, 2), idesc_qk, ks != 0 ? 1u : 0u);
+        }
+        umma_commit<1>(&bar_sfull[st]);
+        umma_commit<1>(&bar_kempty[st]);
+      };
+      mbar_wait(&bar_q, 0);
+      issue_qk(0);
+      for (int j = 0; j < nblk; ++j) {
+        if (j + 1 < nblk) issue_qk(j + 1);                    // overlaps the softmax of block j
+        const int st = j & 1;
+        mbar_wait(&bar_vfull[st], (j >> 1) & 1u);
+        mbar_wait(&bar_pready, j & 1u);                        // P(j) is in smem (and O was rescaled if needed)
+        tc_fence_after();
+        const uint32_t v_addr = smem_base + 3 * kTile + st * kTile;
+#pragma unroll
+        for (int ks = 0; ks < kABN / 16; ++ks) {
+          const uint64_t da = make_smem_desc(p_addr + (ks >> 2) * kPanel + (ks & 3) * 32, 16, 1024, 2);
+          const uint64_t db = make_smem_desc(v_addr + ks * 2048, kPanel, 1024, 2);
+          umma_ss<1>(tO, da, db, idesc_pv, (j | ks) != 0 ? 1u : 0u);
+        }
+        umma_commit<1>(&bar_pvdone);
+        umma_commit<1>(&bar_vempty[st]);
+      }
+    }
+  } else {
+    // ---------------------------- softmax / correction / epilogue ----------------------------
+    const int q = warp & 3;
+    const int row = q * 32 + lane;                 // query row within the tile == TMEM lane
+    const int qi = q0 + row;                       // global query index
+    const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
+    float m_ref = -INFINITY, l = 0.f;
+    for (int j = 0; j < nblk; ++j) {
+      const int st = j & 1;
+      mbar_wait(&bar_sfull[st], (j >> 1) & 1u);
+      tc_fence_after();
+      const uint32_t tS = tS0 + st * 128 + lane_off;
+      const bool diag = causal && (j == nblk - 1);
+      const int k0 = j * kABN;
+      // pass 1: block row max
+      float bm = -INFINITY;
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        uint32_t r[32];
+        tmem_ld_x32(tS + c * 32, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int e = 0; e < 32; ++e) {
+          float s = __uint_as_float(r[e]) * scale_log2;
+          if (diag && (k0 + c * 32 + e > qi)) s = -INFINITY;
+          bm = fmaxf(bm, s);
+        }
+      }
+      // lazy reference update
+      float alpha = 1.f;
+      const bool need = bm > m_ref + kRescaleThreshold;
+      if (need) {
+        alpha = (m_ref == -INFINITY) ? 0.f : exp2f(m_ref - bm);
+        m_ref = bm;
+        l *= alpha;
+      }
+      // P smem and O are only free once P V of block j-1 has retired
+      if (j > 0) mbar_wait(&bar_pvdone, (j - 1) & 1u);
+      if (j > 0 && __any_sync(0xffffffffu, need)) {
+        tc_fence_after();
+#pragma unroll 1
+        for (int c = 0; c < 4; ++c) {
+          uint32_t r[32];
+          tmem_ld_x32(tO + lane_off + c * 32, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int e = 0; e < 32; ++e) r[e] = __float_as_uint(__uint_as_float(r[e]) * alpha);
+          tmem_st_x16(tO + lane_off + c * 32, r);
+          tmem_st_x16(tO + lane_off + c * 32 + 16, r + 16);
+        }
+        tmem_st_wait();
+      }
+      // pass 2: probabilities -> bf16 -> swizzled smem (K-major panels over the key index)
+      float rs = 0.f;
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        uint32_t r[32];
+        tmem_ld_x32(tS + c * 32, r);
+        tmem_ld_wait();
+        uint32_t pk[16];
+#pragma unroll
+        for (int e = 0; e < 32; e += 2) {
+          float s0 = __uint_as_float(r[e]) * scale_log2, s1 = __uint_as_float(r[e + 1]) * scale_log2;
+          if (diag && (k0 + c * 32 + e > qi)) s0 = -INFINITY;
+          if (diag && (k0 + c * 32 + e + 1 > qi)) s1 = -INFINITY;
+          const float p0 = exp2f(s0 - m_ref), p1 = exp2f(s1 - m_ref);
+          rs += p0 + p1;
+          pk[e >> 1] = pack_bf16x2(p0, p1);
+        }
+        // 32 keys = 64 bytes = 4 chunks of 16 B; key index c*32 .. c*32+31 -> panel c/2, chunks (c%2)*4 .. +3
+        uint8_t* prow = sP + (c >> 1) * kPanel + row * 128;
+#pragma unroll
+        for (int ch = 0; ch < 4; ++ch) {
+          const int chunk = (c & 1) * 4 + ch;
+          *reinterpret_cast<uint4*>(prow + ((chunk ^ (row & 7)) << 4)) =
+              make_uint4(pk[ch * 4], pk[ch * 4 + 1], pk[ch * 4 + 2], pk[ch * 4 + 3]);
+        }
+      }
+      l += rs;
+      // S[st] has been fully read; P is written: publish both
+      tc_fence_before();
+      fence_proxy_async_smem();            // generic-proxy smem writes -> visible to the tensor core (async proxy)
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive(&bar_sfree[st]);
+        mbar_arrive(&bar_pready);
+      }
+    }
+    // ---- epilogue: O / l -> bf16 -> global; LSE ----
+    mbar_wait(&bar_pvdone, (nblk - 1) & 1u);
+    tc_fence_after();
+    const float inv_l = 1.f / l;
+    __nv_bfloat16* orow = O + (static_cast<long long>(tok0 + qi)) * o_tok_stride + head * kAD;
+#pragma unroll 1
+    for (int c = 0; c < 4; ++c) {
+      uint32_t r[32];
+      tmem_ld_x32(tO + lane_off + c * 32, r);
+      tmem_ld_wait();
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        float f[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(r[g * 8 + e]) * inv_l;
+        store8(orow + c * 32 + g * 8, pack8(f));
+      }
+    }
+    if (lse != nullptr)
+      lse[(static_cast<long long>(b) * H + head) * S + qi] = (m_ref + log2f(l)) * 0.6931471805599453f;
+    (void)scale;
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<1>(tmem_base, 512);
+  }
+}
+
+}  // namespace llmctl
+
+using namespace llmctl;
+
+// q,k,v: [B, S, H, 128] bf16 views with a common layout: element (b,s,h,d) at ((b*S+s)*tok_stride + h*128 + d).
+// o: same indexing with o_tok_stride.  lse: fp32 [B, H, S] (may be NULL).  S must be a multiple of 128.
+LLMCTL_API int llmctl_flash_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int B,
+                                     int S, int H, int D, long long q_tok_stride, long long k_tok_stride,
+                                     long long v_tok_stride, long long o_tok_stride, float scale, int causal,
+                                     void* stream) {
+  LLMCTL_BEGIN();
+  LLMCTL_REQUIRE(D == kAD && S % kABM == 0 && B > 0 && H > 0);
+  LLMCTL_REQUIRE(q_tok_stride % 8 == 0 && k_tok_stride % 8 == 0 && v_tok_stride % 8 == 0 && o_tok_stride % 8 == 0);
+  CUtensorMap tq, tk, tv;
+  const uint64_t rows = static_cast<uint64_t>(B) * S;
+  int rc = get_tmap_3d_bf16(&tq, q, kAD, H, rows, kAD, q_tok_stride, 64, 1, kABM, 1);
+  if (rc) LLMCTL_FAIL(rc, "tensor map Q");
+  rc = get_tmap_3d_bf16(&tk, k, kAD, H, rows, kAD, k_tok_stride, 64, 1, kABN, 1);
+  if (rc) LLMCTL_FAIL(rc, "tensor map K");
+  rc = get_tmap_3d_bf16(&tv, v, kAD, H, rows, kAD, v_tok_stride, 64, 1, kABN, 1);
+  if (rc) LLMCTL_FAIL(rc, "tensor map V");
+  LLMCTL_CHECK(cudaFuncSetAttribute(flash_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttnSmem));
+  dim3 grid(S / kABM, H, B);
+  flash_fwd_kernel<<<grid, kAttnThreads, kAttnSmem, (cudaStream_t)stream>>>(
+      tq, tk, tv, (__nv_bfloat16*)o, o_tok_stride, lse, S, H, scale * 1.4426950408889634f, scale, causal);
+  LLMCTL_RETURN_LAST();
+}

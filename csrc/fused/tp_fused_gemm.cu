@@ -39,6 +39,9 @@ constexpr int kFSmem = kFStages * kFStageBytes + 1024;
 constexpr int kFThreads = 192;
 constexpr int kCopyPiece = 32768;            // bytes per TMA bulk copy
 constexpr int kCopyStages = 4;               // smem ring of the copy CTAs (4 x 32 KB)
+constexpr int kEpiRowBytes = 128 + 16;       // K2 epilogue staging: 64 bf16 per row + pad (conflict-free 16 B access)
+constexpr int kEpiWarpBytes = 32 * kEpiRowBytes;
+constexpr int kFSmemRS = kFSmem + 4 * kEpiWarpBytes;
 
 __device__ __forceinline__ void bulk_store_1d(void* gdst, const void* smem_src, uint32_t bytes) {
   asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(
@@ -256,6 +259,43 @@ tp_fused_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
       } else {
         crow = C + static_cast<long long>(row) * ldc + n0;
       }
+      if (kMode == 2) {
+        // Remote stores must be wide: stage 64 columns of the warp's 32 rows in shared memory (row = lane), then
+        // let 8 consecutive lanes write one row's 128 contiguous bytes -> full-size NVLink write packets.
+        uint8_t* st = smem + kFStages * kFStageBytes + q * kEpiWarpBytes;
+        __nv_bfloat16* owner_base = reinterpret_cast<__nv_bfloat16*>(xg.ptr[crank]) +
+                                    static_cast<long long>(a.rank) * Ms * a.N;
+#pragma unroll 1
+        for (int hc = 0; hc < kFBN / 64; ++hc) {
+#pragma unroll
+          for (int c2 = 0; c2 < 2; ++c2) {
+            uint32_t r[32];
+            tmem_ld_x32(t_row + hc * 64 + c2 * 32, r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              float f[8];
+#pragma unroll
+              for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(r[j * 8 + e]);
+              const bf16x8 pk = pack8(f);
+              *reinterpret_cast<uint4*>(st + lane * kEpiRowBytes + (c2 * 4 + j) * 16) = *reinterpret_cast<const uint4*>(&pk);
+            }
+          }
+          __syncwarp();
+          const int seg = lane & 7;
+#pragma unroll
+          for (int it = 0; it < 8; ++it) {
+            const int rr = it * 4 + (lane >> 3);
+            const int grow = m0 + q * 32 + rr;
+            const int col = n0 + hc * 64 + seg * 8;
+            if (grow < m_end && grow < a.M && col < a.N) {
+              const uint4 v = *reinterpret_cast<const uint4*>(st + rr * kEpiRowBytes + seg * 16);
+              st_v4(owner_base + static_cast<long long>(grow - crank * Ms) * a.N + col, v);
+            }
+          }
+          __syncwarp();
+        }
+      } else {
 #pragma unroll 1
       for (int c = 0; c < kFBN / 32; ++c) {
         uint32_t r[32];
@@ -269,12 +309,11 @@ tp_fused_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
               float f[8];
 #pragma unroll
               for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(r[j * 8 + e]);
-              const bf16x8 pk = pack8(f);
-              if (kMode == 2) st_v4(crow + c * 32 + j * 8, *reinterpret_cast<const uint4*>(&pk));
-              else store8(crow + c * 32 + j * 8, pk);
+              store8(crow + c * 32 + j * 8, pack8(f));
             }
           }
         }
+      }
       }
       tc_fence_before();
       __syncwarp();
@@ -423,13 +462,13 @@ LLMCTL_API int llmctl_gemm_rs(const void* X, const void* W, llmctl::symm::PeerTa
   rc = get_tmap_2d_bf16(&tmB, W, N, K, ldw, kFBN, kFBK, 1);
   if (rc) LLMCTL_FAIL(rc, "tensor map B");
   auto kern = tp_fused_gemm_kernel<2>;
-  LLMCTL_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kFSmem));
+  LLMCTL_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kFSmemRS));
   FusedArgs a{M, N, K, rank, world, M / world, epoch, 0};
   const int Ms = M / world;
   const int tiles = ((Ms + kFBM - 1) / kFBM) * ((N + kFBN - 1) / kFBN) * world;
   int grid = fused_num_sms();
   if (tiles < grid) grid = tiles;
-  kern<<<grid, kFThreads, kFSmem, (cudaStream_t)stream>>>(tmA, tmB, nullptr, 0, a, stage, pads, local_flags);
+  kern<<<grid, kFThreads, kFSmemRS, (cudaStream_t)stream>>>(tmA, tmB, nullptr, 0, a, stage, pads, local_flags);
   LLMCTL_RETURN_LAST();
 }
 

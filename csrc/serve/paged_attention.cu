@@ -72,33 +72,46 @@ paged_attn_decode_kernel(const __nv_bfloat16* __restrict__ q, long long q_stride
   for (int j = 0; j < 8; ++j) acc[j] = 0.f;
 
   const int rows_per_iter = 4 * kRowsPerWarp;
+  constexpr int kUnroll = 4;     // tokens per group per iteration: 8 independent 16-byte loads in flight per lane
   // The trip count must be uniform across the warp: the shuffles below use the full mask, so a lane whose token
   // is out of range still executes them (with a masked score) instead of leaving the loop early.
-  for (int tb = t0 + warp * kRowsPerWarp; tb < t1; tb += rows_per_iter) {
-    const int t = tb + sub;
-    const bool valid = t < t1;
-    float kf[8], vf[8];
-    if (valid) {
-      const long long slot = static_cast<long long>(bt[t / block_size]) * block_size + (t % block_size);
-      unpack8(load8(k_cache + slot * row_elems + head * kHeadDim + li * 8), kf);
-      unpack8(load8(v_cache + slot * row_elems + head * kHeadDim + li * 8), vf);
-    } else {
+  for (int tb = t0 + warp * kRowsPerWarp; tb < t1; tb += rows_per_iter * kUnroll) {
+    bf16x8 kraw[kUnroll], vraw[kUnroll];
+    bool valid[kUnroll];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) kf[j] = vf[j] = 0.f;
+    for (int u = 0; u < kUnroll; ++u) {
+      const int t = tb + u * rows_per_iter + sub;
+      valid[u] = t < t1;
+      if (valid[u]) {
+        const long long slot = static_cast<long long>(bt[t / block_size]) * block_size + (t % block_size);
+        kraw[u] = load8(k_cache + slot * row_elems + head * kHeadDim + li * 8);
+        vraw[u] = load8(v_cache + slot * row_elems + head * kHeadDim + li * 8);
+      }
     }
-    float s = 0.f;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) s += qf[j] * kf[j];
+    for (int u = 0; u < kUnroll; ++u) {
+      float kf[8], vf[8];
+      if (valid[u]) {
+        unpack8(kraw[u], kf);
+        unpack8(vraw[u], vf);
+      } else {
 #pragma unroll
-    for (int o = kLanesPerRow / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-    if (valid) {
-      const float m_new = fmaxf(m, s);
-      const float corr = exp2f(m - m_new);
-      const float p = exp2f(s - m_new);
-      l = l * corr + p;
+        for (int j = 0; j < 8; ++j) kf[j] = vf[j] = 0.f;
+      }
+      float s = 0.f;
 #pragma unroll
-      for (int j = 0; j < 8; ++j) acc[j] = acc[j] * corr + p * vf[j];
-      m = m_new;
+      for (int j = 0; j < 8; ++j) s += qf[j] * kf[j];
+#pragma unroll
+      for (int o = kLanesPerRow / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+      if (valid[u]) {
+        const float m_new = fmaxf(m, s);
+        const float corr = exp2f(m - m_new);
+        const float pr = exp2f(s - m_new);
+        l = l * corr + pr;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = acc[j] * corr + pr * vf[j];
+        m = m_new;
+      }
     }
   }
 

@@ -33,8 +33,8 @@ def kv_append(qkv: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, s
 
 
 def choose_splits(batch: int, heads: int, max_context: int, block_size: int, sms: int = 148) -> int:
-    want = max(1, (2 * sms + batch * heads - 1) // (batch * heads))
-    return int(max(1, min(want, max(1, max_context // max(4 * block_size, 64)), 32)))
+    want = max(1, (4 * sms + batch * heads - 1) // (batch * heads))          # ~4 CTAs per SM keeps HBM busy
+    return int(max(1, min(want, max(1, max_context // max(4 * block_size, 64)), 64)))
 
 
 def paged_attention_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,

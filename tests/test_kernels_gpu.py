@@ -201,3 +201,33 @@ def test_linear_autograd(cuda_device):
     _close(y, yf, 5e-2, 2e-2, "y")
     _close(x.grad, xf.grad, 5e-2, 2e-2, "dx")
     _close(w.grad, wf.grad, 0.5, 2e-2, "dw")
+
+
+@pytest.mark.parametrize("B,S,H", [(2, 512, 4), (1, 2048, 2), (3, 128, 1), (1, 1024, 8)])
+@pytest.mark.parametrize("packed", [True, False])
+def test_flash_attention_fwd(cuda_device, B, S, H, packed):
+    """tcgen05 flash attention forward vs fp32 softmax(QK^T/sqrt(d))V with a causal mask."""
+    from llmctl_b200.ops import attention as attn, native
+    if not native.has_symbol("llmctl_flash_attn_fwd"):
+        pytest.skip("flash attention kernel not built")
+    D = 128
+    torch.manual_seed(9)
+    if packed:
+        qkv = torch.randn(B, S, 3, H, D, device=cuda_device).bfloat16()
+        q, k, v = qkv[:, :, 0], qkv[:, :, 1], qkv[:, :, 2]
+    else:
+        q, k, v = (torch.randn(B, S, H, D, device=cuda_device).bfloat16() for _ in range(3))
+    assert attn._native_ok(q, k, v)
+    with torch.no_grad():
+        o = attn.attention(q, k, v, causal=True)
+    qf, kf, vf = (t.float().transpose(1, 2) for t in (q, k, v))
+    s = qf @ kf.transpose(-1, -2) / math.sqrt(D)
+    mask = torch.triu(torch.ones(S, S, dtype=torch.bool, device=cuda_device), 1)
+    s = s.masked_fill(mask, float("-inf"))
+    ref = (torch.softmax(s, -1) @ vf).transpose(1, 2)
+    _close(o, ref, 2e-2, 2e-2, "attention out")
+    lse = torch.empty(B, H, S, dtype=torch.float32, device=cuda_device)
+    o2 = torch.empty(B, S, H, D, dtype=torch.bfloat16, device=cuda_device)
+    native.call("llmctl_flash_attn_fwd", q.data_ptr(), k.data_ptr(), v.data_ptr(), o2.data_ptr(), lse.data_ptr(), B, S, H, D,
+                q.stride(1), k.stride(1), v.stride(1), o2.stride(1), 1.0 / math.sqrt(D), 1, native.stream_ptr())
+    _close(lse, torch.logsumexp(s, -1), 2e-2, 1e-3, "lse")
