@@ -78,7 +78,7 @@ reduce_scatter_pull_kernel(PeerTable in, long long n_vec_per_rank, __nv_bfloat16
 #pragma unroll
     for (int r = 0; r < kMaxRanks; ++r) {
       if (r < world) {
-        const uint4* base = reinterpret_cast<const uint4*>(in.ptr[(rank + r) % world]) + rank * n_vec_per_rank;
+        const uint4* base = reinterpret_cast<const uint4*>(in.ptr[r]) + rank * n_vec_per_rank;
         raw0[r] = ptx::ld_nc_v4(base + v0);
         if (has1) raw1[r] = ptx::ld_nc_v4(base + v1);
       }
@@ -86,17 +86,16 @@ reduce_scatter_pull_kernel(PeerTable in, long long n_vec_per_rank, __nv_bfloat16
     float s0[8], s1[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) s0[j] = s1[j] = 0.f;
-    // fixed summation order (rank 0 .. world-1) regardless of the staggered load order -> deterministic
+    // fixed summation order (rank 0 .. world-1) -> deterministic
 #pragma unroll
     for (int rr = 0; rr < kMaxRanks; ++rr) {
       if (rr < world) {
-        const int slot_r = (rr - rank + world) % world;      // where rank rr's data sits in raw[]
         float f[8];
-        unpack8(*reinterpret_cast<const bf16x8*>(&raw0[slot_r]), f);
+        unpack8(*reinterpret_cast<const bf16x8*>(&raw0[rr]), f);
 #pragma unroll
         for (int j = 0; j < 8; ++j) s0[j] += f[j];
         if (has1) {
-          unpack8(*reinterpret_cast<const bf16x8*>(&raw1[slot_r]), f);
+          unpack8(*reinterpret_cast<const bf16x8*>(&raw1[rr]), f);
 #pragma unroll
           for (int j = 0; j < 8; ++j) s1[j] += f[j];
         }

@@ -1,9 +1,10 @@
 """Activation checkpointing: ``none | selective | full``.
 
 * ``full``      — every transformer block is recomputed in backward (only its inputs are kept).
-* ``selective`` — only cheap memory-bound producers are recomputed: the normalised activations and the
-  SwiGLU product are not stored; the GEMM outputs (qkv, attention out, gate|up) are kept.  Implemented by
-  ``NormLinear`` / ``SwiGLULinear`` fused autograd functions below.
+* ``selective`` — only cheap memory-bound producers are recomputed: the SwiGLU product (tokens x ffn, the
+  largest saved tensor of a block) is not stored and is re-derived from the kept gate|up GEMM output in
+  backward (``ops.functional.swiglu_linear``); the attention core already stores only O and the row
+  log-sum-exp (flash attention), and all GEMM outputs are kept.
 * ``none``      — store everything.
 
 Reference: ``activation_checkpoint = "selective"`` is a config string with no consumer

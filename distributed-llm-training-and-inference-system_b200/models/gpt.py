@@ -72,6 +72,7 @@ class MLP(nn.Module):
         super().__init__()
         st = get_state()
         self.gated = cfg.gated
+        self.selective_recompute = False
         self.f_local = cfg.ffn // st.tp
         up_out = 2 * cfg.ffn if self.gated else cfg.ffn
         self.up = tpl.ColumnParallelLinear(cfg.hidden, up_out, std=cfg.init_std, dtype=dtype, device=device,
@@ -81,6 +82,9 @@ class MLP(nn.Module):
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         gu = self.up(x)
+        if self.gated and self.selective_recompute and torch.is_grad_enabled():
+            # selective activation checkpointing: the SwiGLU product is recomputed in backward
+            return self.down.finish(ops.swiglu_linear(gu, self.down.weight, recompute=True))
         act = ops.swiglu(gu) if self.gated else F.gelu(gu)
         return self.down(act)
 
@@ -120,6 +124,8 @@ class GPTModel(nn.Module):
             self.embed = tpl.VocabParallelEmbedding(self.vocab_padded, cfg.hidden, std=cfg.init_std, dtype=dtype,
                                                     device=device)
         self.blocks = nn.ModuleList([Block(cfg, dtype, device) for _ in range(lo, hi)])
+        for blk in self.blocks:
+            blk.mlp.selective_recompute = activation_checkpoint == "selective"
         if self.is_last:
             self.final_norm = Norm(cfg, dtype, device)
             if cfg.tie_word_embeddings and self.is_first:

@@ -384,6 +384,57 @@ def linear(x: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
     return F.linear(x, w)
 
 
+class _SwiGLULinearFn(torch.autograd.Function):
+    """``swiglu(gate_up) @ w.T`` that stores only ``gate_up``: the SwiGLU product (the down-projection's input,
+    tokens x ffn) is recomputed in backward.  This is the "selective" activation-checkpointing policy."""
+
+    @staticmethod
+    def forward(ctx, gu, w):
+        M, F2 = gu.shape
+        act = torch.empty(M, F2 // 2, dtype=gu.dtype, device=gu.device)
+        native.call("llmctl_swiglu_fwd", gu.data_ptr(), act.data_ptr(), M, F2 // 2, gu.stride(0), native.stream_ptr())
+        y = gemm_raw(act, w)
+        ctx.save_for_backward(gu, w)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        gu, w = ctx.saved_tensors
+        M, F2 = gu.shape
+        if not _gemm_ok(dy):
+            dy = dy.contiguous()
+        act = torch.empty(M, F2 // 2, dtype=gu.dtype, device=gu.device)          # recompute
+        native.call("llmctl_swiglu_fwd", gu.data_ptr(), act.data_ptr(), M, F2 // 2, gu.stride(0), native.stream_ptr())
+        dact = gemm_raw(dy, w, b_mn=True)
+        dgu = torch.empty_like(gu)
+        native.call("llmctl_swiglu_bwd", dact.data_ptr(), gu.data_ptr(), dgu.data_ptr(), M, F2 // 2, gu.stride(0),
+                    native.stream_ptr())
+        dw = None
+        mg = getattr(w, "main_grad", None)
+        if mg is not None:
+            fresh = getattr(w, "_main_grad_fresh", False)
+            gemm_raw(dy, act, a_mn=True, b_mn=True, out=mg, accumulate=not fresh)
+            w._main_grad_fresh = False
+            cb = getattr(w, "_grad_ready_cb", None)
+            if cb is not None:
+                cb(w)
+        else:
+            dw = gemm_raw(dy, act, a_mn=True, b_mn=True)
+        return dgu, dw
+
+
+def swiglu_linear(gate_up: torch.Tensor, w: torch.Tensor, recompute: bool = True) -> torch.Tensor:
+    """``swiglu(gate_up) @ w.T``; with ``recompute`` the activation is not kept for backward."""
+    g2 = gate_up.reshape(-1, gate_up.shape[-1])
+    if (recompute and _use_native(g2, "elementwise") and _cfg.gemm == "native" and w.dtype == torch.bfloat16
+            and g2.shape[-1] % 16 == 0 and _gemm_ok(g2, w) and w.shape[0] % 8 == 0):
+        return _SwiGLULinearFn.apply(g2, w).view(*gate_up.shape[:-1], w.shape[0])
+    if recompute and torch.is_grad_enabled() and gate_up.requires_grad:
+        from torch.utils.checkpoint import checkpoint
+        return linear(checkpoint(swiglu, gate_up, use_reentrant=False), w)
+    return linear(swiglu(gate_up), w)
+
+
 # ------------------------------------------------------------------------------------------------
 # Cross entropy (K15)
 # ------------------------------------------------------------------------------------------------

@@ -188,10 +188,14 @@ class RowParallelLinear(nn.Module):
             from ..comms import fused
             if fused.enabled(x):
                 return fused.linear_rs(x, self.weight)
-        y = ops.linear(x, self.weight)
+        return self.finish(ops.linear(x, self.weight))
+
+    def finish(self, y_local: torch.Tensor) -> torch.Tensor:
+        """Reduce the per-rank partial product (all-reduce, or reduce-scatter over tokens with SP)."""
+        st = get_state()
         if st.tp > 1:
-            y = reduce_scatter_seq(y) if st.sequence_parallel else reduce_from_tp(y)
-        return y
+            return reduce_scatter_seq(y_local) if st.sequence_parallel else reduce_from_tp(y_local)
+        return y_local
 
 
 class VocabParallelEmbedding(nn.Module):

@@ -231,3 +231,27 @@ def test_flash_attention_fwd(cuda_device, B, S, H, packed):
     native.call("llmctl_flash_attn_fwd", q.data_ptr(), k.data_ptr(), v.data_ptr(), o2.data_ptr(), lse.data_ptr(), B, S, H, D,
                 q.stride(1), k.stride(1), v.stride(1), o2.stride(1), 1.0 / math.sqrt(D), 1, native.stream_ptr())
     _close(lse, torch.logsumexp(s, -1), 2e-2, 1e-3, "lse")
+
+
+@pytest.mark.parametrize("B,S,H", [(2, 256, 2), (1, 1024, 4), (2, 128, 1)])
+def test_flash_attention_bwd(cuda_device, B, S, H):
+    """tcgen05 flash attention backward (dq, dk, dv) vs autograd through the fp32 reference."""
+    from llmctl_b200.ops import attention as attn, native
+    if not native.has_symbol("llmctl_flash_attn_bwd"):
+        pytest.skip("flash attention backward kernel not built")
+    D = 128
+    torch.manual_seed(10)
+    qkv = (0.5 * torch.randn(B, S, 3, H, D, device=cuda_device)).bfloat16().requires_grad_(True)
+    q, k, v = qkv[:, :, 0], qkv[:, :, 1], qkv[:, :, 2]
+    o = attn.attention(q, k, v, causal=True)
+    do = torch.randn_like(o)
+    o.backward(do)
+    ref_in = qkv.detach().float().requires_grad_(True)
+    qf, kf, vf = (ref_in[:, :, i].transpose(1, 2) for i in range(3))
+    s = qf @ kf.transpose(-1, -2) / math.sqrt(D)
+    s = s.masked_fill(torch.triu(torch.ones(S, S, dtype=torch.bool, device=cuda_device), 1), float("-inf"))
+    ref = (torch.softmax(s, -1) @ vf).transpose(1, 2)
+    ref.backward(do.float())
+    _close(o, ref, 2e-2, 2e-2, "out")
+    for i, name in enumerate(("dq", "dk", "dv")):
+        _close(qkv.grad[:, :, i], ref_in.grad[:, :, i], 4e-2, 4e-2, name)

@@ -199,3 +199,22 @@ def test_dataset_determinism_and_resume():
     nxt, _ = a.next_batch()
     c = TokenLoader(ds, 2, dp_rank=0, dp_size=2); c.load_state_dict(st)
     assert torch.equal(c.next_batch()[0], nxt)                                         # resumable cursor
+
+
+def test_shipped_configs_validate():
+    """Every file under configs/ parses with its schema; the 13B 3D preset plans onto 8 GPUs."""
+    from pathlib import Path
+    from llmctl_b200.config.schemas import load_hardware_profile, load_model_file, load_training_preset
+    from llmctl_b200.models.config import ModelConfig
+    root = Path(__file__).resolve().parent.parent / "configs"
+    for f in (root / "models").glob("*.json"):
+        m = load_model_file(f)
+        assert ModelConfig.from_file(f).num_parameters() == m.estimated_params
+    hw = load_hardware_profile(root / "hw" / "b200x8.toml")
+    assert hw.gpu.count == 8 and hw.limits.measured and hw.interconnect.nvls_multicast
+    names = set()
+    for f in (root / "presets").glob("*.toml"):
+        p = load_training_preset(f)
+        names.add(f.name)
+        assert p.parallel.tensor_parallel * p.parallel.pipeline_parallel <= 8
+    assert {"gpt-7b-b200x8-tp8-sp.toml", "gpt-7b-b200x8-zero3.toml", "gpt-13b-b200x8-tp4-pp2.toml", "gpt-125m-cpu-pp2.toml"} <= names
