@@ -97,44 +97,72 @@ tp_fused_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
           signal_set(reinterpret_cast<uint32_t*>(pads.ptr[p]) + a.rank, a.epoch);
       const long long chunk_bytes = static_cast<long long>(Ms) * a.K * 2;
       const int pieces = static_cast<int>((chunk_bytes + kCopyPiece - 1) / kCopyPiece);
+      // This CTA's work list, chunk-major in ring order: item w -> (chunk i = 1 + w / per_cta, piece).  Loads are
+      // issued kCopyStages ahead of the stores and the pipeline is never drained between chunks; a chunk is
+      // published once all of this CTA's stores for it are known complete (cp.async.bulk.wait_group) — the last of
+      // the n_copy CTAs to get there raises chunk_ready.
+      const int per_cta = (pieces - static_cast<int>(blockIdx.x) + a.n_copy - 1) / a.n_copy;   // my pieces per chunk
+      const int total = per_cta * (a.world - 1);
       uint32_t phase_bits = 0;
-      int issued = 0;       // pieces issued by this CTA (ring position)
-      for (int i = 1; i < a.world; ++i) {
-        const int src = (a.rank + i) % a.world;
-        signal_wait_ge(reinterpret_cast<const uint32_t*>(pads.ptr[a.rank]) + src, a.epoch);
-        const uint8_t* gsrc = reinterpret_cast<const uint8_t*>(xg.ptr[src]) + static_cast<long long>(src) * chunk_bytes;
-        uint8_t* gdst = reinterpret_cast<uint8_t*>(xg.ptr[a.rank]) + static_cast<long long>(src) * chunk_bytes;
-        // software pipeline over this CTA's pieces: keep up to kCopyStages loads in flight
-        int head = blockIdx.x, tail = blockIdx.x;     // piece indices (stride n_copy)
-        int in_flight = 0;
-        while (tail < pieces) {
-          while (head < pieces && in_flight < kCopyStages) {
-            const int slot = issued % kCopyStages;
-            tma_store_wait_read<0>();   // every earlier smem->global store has finished READING its slot
-            const long long off = static_cast<long long>(head) * kCopyPiece;
-            const uint32_t bytes = static_cast<uint32_t>(min(static_cast<long long>(kCopyPiece), chunk_bytes - off));
-            mbar_expect_tx(&bar_copy[slot], bytes);
-            bulk_load_1d(smem + slot * kCopyPiece, gsrc + off, bytes, &bar_copy[slot]);
-            ++issued; ++in_flight; head += a.n_copy;
+      int issued = 0, stored = 0, published = 0;      // work-item counters; `published` counts whole chunks
+      int waited_chunk = 0;                            // peers whose "rows ready" flag has been observed (1-based ring index)
+      auto item = [&](int w, int& src, long long& off, uint32_t& bytes) {
+        const int ci = 1 + w / per_cta;
+        src = (a.rank + ci) % a.world;
+        const int piece = static_cast<int>(blockIdx.x) + (w % per_cta) * a.n_copy;
+        off = static_cast<long long>(piece) * kCopyPiece;
+        bytes = static_cast<uint32_t>(min(static_cast<long long>(kCopyPiece), chunk_bytes - off));
+      };
+      auto publish_upto = [&](int n_chunks_done) {
+        while (published < n_chunks_done) {
+          const int src = (a.rank + 1 + published) % a.world;
+          __threadfence();
+          const uint32_t done = atomicAdd(&local_flags[16 + src], 1u) + 1u;
+          if (done == static_cast<uint32_t>(a.n_copy)) {
+            atomicExch(&local_flags[16 + src], 0u);
+            st_release_gpu(&local_flags[src], a.epoch);
           }
-          const int slot = (issued - in_flight) % kCopyStages;
+          ++published;
+        }
+      };
+      if (per_cta == 0) {
+        publish_upto(a.world - 1);                     // nothing to copy: still take part in the chunk counters
+      } else {
+        while (stored < total) {
+          while (issued < total && issued - stored < kCopyStages) {
+            int src; long long off; uint32_t bytes;
+            item(issued, src, off, bytes);
+            const int ci = 1 + issued / per_cta;
+            if (ci > waited_chunk) {                   // first touch of this peer: its rows must be in place
+              signal_wait_ge(reinterpret_cast<const uint32_t*>(pads.ptr[a.rank]) + src, a.epoch);
+              waited_chunk = ci;
+            }
+            const int slot = issued % kCopyStages;
+            tma_store_wait_read<0>();                 // every earlier smem->global store has finished READING its slot
+            mbar_expect_tx(&bar_copy[slot], bytes);
+            bulk_load_1d(smem + slot * kCopyPiece,
+                         reinterpret_cast<const uint8_t*>(xg.ptr[src]) + static_cast<long long>(src) * chunk_bytes + off,
+                         bytes, &bar_copy[slot]);
+            ++issued;
+          }
+          int src; long long off; uint32_t bytes;
+          item(stored, src, off, bytes);
+          const int slot = stored % kCopyStages;
           mbar_wait(&bar_copy[slot], (phase_bits >> slot) & 1u);
           phase_bits ^= (1u << slot);
-          const long long off = static_cast<long long>(tail) * kCopyPiece;
-          const uint32_t bytes = static_cast<uint32_t>(min(static_cast<long long>(kCopyPiece), chunk_bytes - off));
-          fence_proxy_async_smem();
-          bulk_store_1d(gdst + off, smem + slot * kCopyPiece, bytes);
+          bulk_store_1d(reinterpret_cast<uint8_t*>(xg.ptr[a.rank]) + static_cast<long long>(src) * chunk_bytes + off,
+                        smem + slot * kCopyPiece, bytes);
           tma_store_commit();
-          --in_flight; tail += a.n_copy;
+          ++stored;
+          // chunks whose last store is older than the kCopyStages most recent groups are complete after this wait
+          const int safe_items = stored - kCopyStages;
+          if (safe_items > 0 && safe_items / per_cta > published) {
+            tma_store_wait<kCopyStages>();
+            publish_upto(safe_items / per_cta);
+          }
         }
-        tma_store_wait<0>();                             // this CTA's part of chunk `src` is in local memory
-        __threadfence();
-        // last copy CTA to finish the chunk publishes it
-        const uint32_t done = atomicAdd(&local_flags[16 + src], 1u) + 1u;
-        if (done == static_cast<uint32_t>(a.n_copy)) {
-          atomicExch(&local_flags[16 + src], 0u);
-          st_release_gpu(&local_flags[src], a.epoch);
-        }
+        tma_store_wait<0>();
+        publish_upto(a.world - 1);
       }
     }
     return;
@@ -439,7 +467,7 @@ LLMCTL_API int llmctl_ag_gemm(llmctl::symm::PeerTable xg, const void* W, void* C
   auto kern = tp_fused_gemm_kernel<1>;
   LLMCTL_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kFSmem));
   if (world == 1) n_copy = 0;
-  else if (n_copy <= 0) n_copy = 12;
+  else if (n_copy <= 0) n_copy = (world > 2) ? 28 : 16;
   FusedArgs a{M, N, K, rank, world, M / world, epoch, n_copy};
   const int grid = fused_num_sms();
   kern<<<grid, kFThreads, kFSmem, (cudaStream_t)stream>>>(tmA, tmB, (__nv_bfloat16*)C, ldc, a, xg, pads,

@@ -25,6 +25,7 @@ Reference: ZeRO exists only as the integer ``zero_stage`` (reference llmctl/cli/
 from __future__ import annotations
 
 import math
+import warnings
 from typing import Callable, Dict, Iterable, List, Optional, Sequence
 
 import torch
@@ -33,6 +34,9 @@ import torch.nn as nn
 
 from ..comms.mesh import ParallelState, get_state
 from ..ops import optim as fused_optim
+
+# the embedding unit has no differentiable input: its pre-backward hook fires on output grads, which is intended
+warnings.filterwarnings("ignore", message="Full backward hook is firing when gradients are computed with respect to module outputs")
 
 _ALIGN = 128  # elements; keeps every parameter view 256-byte aligned (TMA needs 16)
 
@@ -128,13 +132,20 @@ class ParamUnit:
         """ZeRO-3: materialise the full parameters from the shards (no-op if resident)."""
         if self.flat_param is not None:
             return
-        flat = torch.empty(self.numel, dtype=self.dtype, device=self.device)
-        dist.all_gather_into_tensor(flat, self.param_shard, group=self.st.dp_group)
+        gatherer = getattr(self, "_gatherer", None)
+        if gatherer is not None:
+            flat = gatherer.gather(self)
+        else:
+            flat = torch.empty(self.numel, dtype=self.dtype, device=self.device)
+            dist.all_gather_into_tensor(flat, self.param_shard, group=self.st.dp_group)
         self.flat_param = flat
         self._bind_params(flat)
 
     def release_params(self) -> None:
         if self.zero_stage >= 3 and self.dp > 1 and self.flat_param is not None:
+            gatherer = getattr(self, "_gatherer", None)
+            if gatherer is not None:
+                gatherer.release(self)
             self._release_params()
 
     # ---- gradient bucket -----------------------------------------------------------------------
@@ -173,6 +184,68 @@ class ParamUnit:
             self._on_ready(self)
 
 
+class PeerParamGatherer:
+    """K8 (first step): ZeRO-3 parameter all-gather over NVLink peer memory with our own pull kernel
+    (``llmctl_allgather_pull``) instead of NCCL, plus prefetch of the next unit on a side stream so the transfer
+    overlaps the current unit's GEMMs.  Units are gathered into a small pool of symmetric buffers (each as large
+    as the biggest unit); a buffer is recycled when its unit is released.  The kernel's own end-of-kernel
+    all-rank handshake makes immediate reuse safe.  (Fusing the gather into the first consuming GEMM, K1-style
+    with the B operand gathered, is listed in DESIGN.md §7.)"""
+
+    def __init__(self, units, st: ParallelState, pool: int = 4):
+        from ..comms.collectives import PeerCollectives
+        self.st = st
+        self.units = units
+        self.max_numel = max(u.numel for u in units)
+        self.pool = [PeerCollectives(self.max_numel, st.dp_group, st.device) for _ in range(pool)]
+        self.free = list(range(pool))
+        self.owner: Dict[str, int] = {}
+        self.pending: Dict[str, torch.cuda.Event] = {}
+        self.stream = torch.cuda.Stream(device=st.device)
+        self.order = {u.name: i for i, u in enumerate(units)}
+        self.direction = +1
+
+    def _launch(self, u: "ParamUnit", stream) -> None:
+        slot = self.free.pop()
+        self.owner[u.name] = slot
+        pc = self.pool[slot]
+        with torch.cuda.stream(stream):
+            chunk = u.shard_numel
+            pc.buf.tensor[pc.rank * chunk:(pc.rank + 1) * chunk].copy_(u.param_shard, non_blocking=True)
+            pc.all_gather_(chunk)
+            ev = torch.cuda.Event()
+            ev.record(stream)
+        self.pending[u.name] = ev
+
+    def prefetch(self, u: "ParamUnit") -> None:
+        if u.name in self.owner or u.flat_param is not None or not self.free:
+            return
+        self.stream.wait_stream(torch.cuda.current_stream(self.st.device))
+        self._launch(u, self.stream)
+
+    def gather(self, u: "ParamUnit") -> torch.Tensor:
+        cur = torch.cuda.current_stream(self.st.device)
+        if u.name not in self.owner:
+            if not self.free:
+                raise RuntimeError("ZeRO-3 gather pool exhausted; release units before gathering more")
+            self._launch(u, cur)
+        ev = self.pending.pop(u.name, None)
+        if ev is not None:
+            cur.wait_event(ev)
+        flat = self.pool[self.owner[u.name]].buf.tensor[:u.numel]
+        # prefetch the unit that will be needed next (forward: next unit, backward: previous unit)
+        i = self.order[u.name] + self.direction
+        if 0 <= i < len(self.units):
+            self.prefetch(self.units[i])
+        return flat
+
+    def release(self, u: "ParamUnit") -> None:
+        slot = self.owner.pop(u.name, None)
+        if slot is not None:
+            self.pending.pop(u.name, None)
+            self.free.append(slot)
+
+
 class ZeroOptimizer:
     """AdamW over ``ParamUnit``s with DP / ZeRO-1/2/3 gradient and parameter collectives."""
 
@@ -208,6 +281,20 @@ class ZeroOptimizer:
                 off += u.numel
                 u.reduced = torch.empty(u.shard_numel, dtype=torch.float32, device=u.device)
             self.units.append(u)
+        self.gatherer = None
+        if (self.zero_stage >= 3 and self.st.dp > 1 and self.st.device.type == "cuda" and comm != "nccl"
+                and self.st.tp == 1 and self.st.pp == 1):
+            try:
+                from ..comms import symm
+                from ..ops import functional as _ops
+                if symm.available() and _ops.kernel_config().optimizer == "native":
+                    self.gatherer = PeerParamGatherer(self.units, self.st)
+                    for u in self.units:
+                        u._gatherer = self.gatherer
+            except Exception as e:  # noqa: BLE001
+                if comm == "native":
+                    raise
+                self.gatherer = None
         self._last_micro = True
         self.use_multicast = False       # NVLS multimem.st for the parameter push (opt-in after validation)
         self._norm_buf = None
@@ -229,6 +316,8 @@ class ZeroOptimizer:
 
     def _pre_backward(self, u: ParamUnit) -> None:
         self._in_backward = True
+        if self.gatherer is not None:
+            self.gatherer.direction = -1
         if self.zero_stage >= 3 and self.st.dp > 1:
             u.gather_params()
         u.ensure_grad_bucket()
@@ -282,6 +371,8 @@ class ZeroOptimizer:
         self._last_micro = index == total - 1
 
     def zero_grad(self) -> None:
+        if self.gatherer is not None:
+            self.gatherer.direction = +1
         for u in self.units:
             u.grad_shard = None
             u._shard_fresh = True

@@ -187,6 +187,28 @@ def case_zero_native(out):
     out["zero_native"] = {"nccl": traj["nccl"], "native": traj["native"], "max_param_diff": dp}
 
 
+def case_zero3_native(out):
+    """K8 first step: ZeRO-3 with the peer-memory parameter gather (+prefetch) vs NCCL all-gathers."""
+    from llmctl_b200.parallel.zero import ZeroOptimizer
+    from llmctl_b200.runtime.engine import LRSchedule
+    traj = {}
+    for comm in ("nccl", "auto"):
+        eng = _engine(dict(zero_stage=3))
+        c = eng.config
+        eng.optimizer = ZeroOptimizer(eng.model, lr=c.learning_rate, betas=tuple(c.betas), eps=c.adam_eps, weight_decay=c.weight_decay,
+                                      zero_stage=3, grad_clip=c.gradient_clipping, state=eng.state, comm=comm)
+        eng.scheduler = LRSchedule(c.learning_rate, 0, 100, "constant")
+        if comm == "auto":
+            assert eng.optimizer.gatherer is not None, "peer gatherer was not enabled"
+        traj[comm] = [eng._reduce_scalar(eng.train_step()["loss"]) for _ in range(4)]
+        from llmctl_b200.comms import mesh
+        torch.cuda.synchronize(); dist.barrier()
+        mesh.reset_state()
+    for a, b in zip(traj["nccl"], traj["auto"]):
+        assert abs(a - b) < 2e-2 * max(1, abs(a)), f"{traj}"
+    out["zero3_native"] = traj
+
+
 def case_tp_sp_engine(out):
     """TP=world + SP training with the fused K1/K2 linears vs the NCCL collectives."""
     from llmctl_b200.comms import fused, mesh
@@ -206,7 +228,8 @@ def case_tp_sp_engine(out):
     out["tp_sp_engine"] = res
 
 
-CASES = {"probe": case_probe, "tp_kernels": case_tp_kernels, "zero_native": case_zero_native, "tp_sp_engine": case_tp_sp_engine}
+CASES = {"probe": case_probe, "tp_kernels": case_tp_kernels, "zero_native": case_zero_native, "zero3_native": case_zero3_native,
+         "tp_sp_engine": case_tp_sp_engine}
 
 
 def main():

@@ -41,3 +41,7 @@ def test_zero_native_matches_nccl(cuda_device):
 
 def test_tp_sp_engine_fused_matches_nccl(cuda_device):
     _run(["tp_sp_engine"])
+
+
+def test_zero3_peer_gather_matches_nccl(cuda_device):
+    _run(["zero3_native"])
