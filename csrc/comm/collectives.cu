@@ -159,6 +159,7 @@ static int comm_grid(long long n_vec, int max_ctas) {
 }  // namespace llmctl
 
 using namespace llmctl;
+LLMCTL_SYMM_WATCHDOG_MODULE(collectives)
 
 // buf: symmetric [world * chunk_bytes]; rank r's chunk is valid on rank r at entry, all chunks valid everywhere at exit.
 LLMCTL_API int llmctl_allgather_pull(llmctl::symm::PeerTable buf, long long chunk_bytes, llmctl::symm::PeerTable pads,

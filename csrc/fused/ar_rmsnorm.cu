@@ -91,6 +91,7 @@ ar_residual_rmsnorm_kernel(PeerTable x, long long x_off, const void* mc_x, PeerT
 }  // namespace llmctl
 
 using namespace llmctl;
+LLMCTL_SYMM_WATCHDOG_MODULE(ar_rmsnorm)
 
 // x: per-rank base pointers of the symmetric partial-sum buffer (bf16), x_off in elements, [rows, cols] each.
 // mc_x: NVLS multicast address of the same buffer or NULL.  slot_base: first of `world` pad slots to use.

@@ -182,6 +182,7 @@ adam_allgather_kernel(PeerTable params, long long bucket_off, void* mc_params, P
 }  // namespace llmctl
 
 using namespace llmctl;
+LLMCTL_SYMM_WATCHDOG_MODULE(rs_adam)
 
 // Pull-reduce this rank's [shard_lo, shard_lo + shard_n) slice of a bf16 bucket from every rank.
 //   grads      : per-rank base pointers of the symmetric gradient buffer; bucket_off = unit offset (elements)

@@ -447,6 +447,7 @@ static int fused_num_sms() {
 }  // namespace llmctl
 
 using namespace llmctl;
+LLMCTL_SYMM_WATCHDOG_MODULE(tp_fused_gemm)
 
 // K1.  xg: symmetric activation buffer [M, K] bf16 on every rank (rank r's rows [r*Ms,(r+1)*Ms) valid on entry,
 // all rows valid locally on exit).  W: [N, K] local weight shard.  C: [M, N] local output.

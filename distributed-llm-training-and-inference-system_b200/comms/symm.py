@@ -84,3 +84,36 @@ class EpochCounter:
     def next(self, name: str) -> int:
         self._e[name] = self._e.get(name, 0) + 1
         return self._e[name]
+
+
+# ---- signal-wait watchdog (device side: csrc/comm/symm.cuh, host side: csrc/comm/watchdog.cu) -----------------
+class CommWatchdogError(RuntimeError):
+    """A kernel gave up waiting for a peer's flag: the step's data is invalid."""
+
+
+def watchdog_poll(clear: bool = True) -> Optional[Dict[str, object]]:
+    """Synchronous read of the per-module watchdog records of the current device.  ``None`` when nothing tripped."""
+    from ..ops import native
+    if not (torch.cuda.is_available() and native.has_symbol("llmctl_comm_watchdog_poll")):
+        return None
+    out = (ctypes.c_ulonglong * 8)()
+    name = ctypes.create_string_buffer(64)
+    native.register_signature("llmctl_comm_watchdog_poll", [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_int, ctypes.c_int])
+    native.call("llmctl_comm_watchdog_poll", ctypes.cast(out, ctypes.c_void_p), name, 64, int(clear))
+    if out[0] == 0:
+        return None
+    return {"timed_out_waits": int(out[0]), "expected_epoch": int(out[1]), "seen": int(out[2]), "block": int(out[3]),
+            "flag_addr": hex(out[4]), "waited_ms": out[5] / 1e6, "module": name.value.decode()}
+
+
+def set_watchdog_timeout_ms(ms: int) -> None:
+    from ..ops import native
+    native.register_signature("llmctl_comm_watchdog_set_timeout_ms", [ctypes.c_ulonglong])
+    native.call("llmctl_comm_watchdog_set_timeout_ms", int(ms))
+
+
+def check_watchdog(context: str = "") -> None:
+    """Raise ``CommWatchdogError`` (with the flag / epoch the kernel was stuck on) if any peer wait timed out."""
+    rec = watchdog_poll(clear=True)
+    if rec is not None:
+        raise CommWatchdogError(f"peer-signal wait timed out{(' during ' + context) if context else ''}: {rec}")

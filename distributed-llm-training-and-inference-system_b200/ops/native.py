@@ -17,6 +17,8 @@ from typing import Optional
 
 import torch
 
+from ..utils import nvtx as _nvtx
+
 _LIB_DIR = Path(__file__).resolve().parent.parent / "lib"
 _LIB_PATH = _LIB_DIR / "libllmctl_b200.so"
 _lock = threading.Lock()
@@ -108,14 +110,20 @@ class NativeError(RuntimeError):
 
 
 #: kernels launched per entry point when it is not exactly one
-_KERNELS_PER_CALL = {"llmctl_rmsnorm_bwd": 2, "llmctl_layernorm_bwd": 3, "llmctl_sumsq": 2}
+_KERNELS_PER_CALL = {"llmctl_rmsnorm_bwd": 2, "llmctl_layernorm_bwd": 3, "llmctl_sumsq": 2, "llmctl_rmsnorm_bwd_noalloc": 2,
+                     "llmctl_flash_attn_bwd": 3, "llmctl_rs_sumsq": 2, "llmctl_paged_attn_decode": 2,
+                     "llmctl_comm_watchdog_poll": 0, "llmctl_comm_watchdog_set_timeout_ms": 0}
 
 
 def call(name: str, *args) -> None:
     """Invoke a C entry point and raise on a non-zero status."""
     global launch_count
     fn = getattr(lib(), name)
-    rc = fn(*args)
+    if _nvtx.KERNEL_RANGES:
+        with _nvtx.nvtx_range(name):
+            rc = fn(*args)
+    else:
+        rc = fn(*args)
     launch_count += _KERNELS_PER_CALL.get(name, 1)
     if rc != 0:
         raise NativeError(f"{name} failed with cudaError {rc}")

@@ -37,6 +37,7 @@ from ..models.gpt import build_model
 from ..ops import functional as ops
 from ..parallel.pp import PipelineSchedule, partition_layers
 from ..parallel.zero import ZeroOptimizer
+from ..utils.nvtx import nvtx_range
 
 log = logging.getLogger("llmctl.engine")
 
@@ -270,8 +271,10 @@ class TrainingEngine:
             for i in range(n_micro):
                 opt.set_micro_batch(i, n_micro)
                 tokens, targets = self.train_dataloader.next_batch()
-                loss = self.model(tokens, targets=targets, loss_scale=scale)
-                loss.backward()
+                with nvtx_range("forward"):
+                    loss = self.model(tokens, targets=targets, loss_scale=scale)
+                with nvtx_range("backward"):
+                    loss.backward()
                 total = loss.detach() if total is None else total + loss.detach()
             return total
         # ---- pipeline: 1F1B ----
@@ -301,8 +304,11 @@ class TrainingEngine:
     def train_step(self) -> Dict[str, torch.Tensor]:
         lr = self.scheduler.lr_at(self.global_step)
         self._maybe_inject_fault()
-        loss = self._forward_backward()
-        gnorm = self.optimizer.step(lr)
+        with nvtx_range(f"step {self.global_step}"):
+            with nvtx_range("forward_backward"):
+                loss = self._forward_backward()
+            with nvtx_range("optimizer_step"):
+                gnorm = self.optimizer.step(lr)
         self.global_step += 1
         return {"loss": loss, "grad_norm": gnorm, "lr": lr}
 
@@ -364,6 +370,7 @@ class TrainingEngine:
                 # the only host sync of the loop: once per logging window
                 loss = self._reduce_scalar(out["loss"])
                 gn = float(out["grad_norm"])
+                self._check_comm_watchdog(f"steps up to {step}")
                 dt = (time.perf_counter() - window_t0) / max(window_steps, 1)
                 last = tracker.log(step, loss, gn, out["lr"], dt)
                 window_t0, window_steps = time.perf_counter(), 0
@@ -387,6 +394,14 @@ class TrainingEngine:
             self.metrics_file.close()
             self.metrics_file = None
         return {"global_step": self.global_step, **last}
+
+    def _check_comm_watchdog(self, context: str) -> None:
+        """Peer-memory kernels give up (instead of hanging the GPU) when a peer's flag never arrives; whatever
+        they produced after that is garbage, so this is checked wherever results leave the device: before a
+        logging window is reported and before a checkpoint is written."""
+        if self.state.device.type == "cuda" and self.state.world_size > 1:
+            from ..comms.symm import check_watchdog
+            check_watchdog(context)
 
     def _reduce_scalar(self, t: torch.Tensor) -> float:
         """Mean over DP of a loss that lives on the last pipeline stage."""
@@ -435,6 +450,9 @@ class TrainingEngine:
     # ---- checkpoints -----------------------------------------------------------------------------------
     def save_checkpoint(self, final: bool = False):
         c = self.config
+        if self.state.device.type == "cuda":
+            torch.cuda.synchronize(self.state.device)
+        self._check_comm_watchdog("the steps before this checkpoint")
         return ckpt_io.save_checkpoint(
             c.output_dir, self.global_step, self.model, self.optimizer, epoch=self.epoch, config=c.to_dict(),
             model_config=self.model_config,

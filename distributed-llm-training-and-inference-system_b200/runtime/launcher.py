@@ -69,6 +69,12 @@ class BaseLauncher(ABC):
         env["PYTHONPATH"] = root + (os.pathsep + env["PYTHONPATH"] if env.get("PYTHONPATH") else "")
         if c.nccl_debug:
             env["NCCL_DEBUG"] = c.nccl_debug
+        # a rank that dies inside a collective must take the job down (torchrun then restarts it from the latest
+        # complete checkpoint) instead of leaving the peers spinning; the flight recorder keeps the last collectives
+        # of every rank for the post-mortem of a pipeline (batch_isend_irecv) hang
+        env.setdefault("TORCH_NCCL_ASYNC_ERROR_HANDLING", "1")
+        env.setdefault("TORCH_NCCL_TRACE_BUFFER_SIZE", "2000")
+        env.setdefault("TORCH_NCCL_DUMP_ON_TIMEOUT", "1")
         if c.deterministic:
             env["PYTHONHASHSEED"] = str(c.seed)
             env["CUBLAS_WORKSPACE_CONFIG"] = ":4096:8"

@@ -228,7 +228,51 @@ def case_tp_sp_engine(out):
     out["tp_sp_engine"] = res
 
 
-CASES = {"probe": case_probe, "tp_kernels": case_tp_kernels, "zero_native": case_zero_native, "zero3_native": case_zero3_native,
+def case_watchdog(out):
+    """A rank that never launches its side of a collective: the waiting kernel must give up after the deadline,
+    report what it was waiting for, and the communicator must be usable again afterwards."""
+    import time
+    from llmctl_b200.comms import symm
+    from llmctl_b200.comms.collectives import PeerCollectives
+    rank, world = dist.get_rank(), dist.get_world_size()
+    pc = PeerCollectives(1 << 16)
+    n = 4096
+    pc.buf.tensor[:n].fill_(float(rank + 1))
+    torch.cuda.synchronize(); dist.barrier()
+    ref = pc.all_reduce(n, algo="oneshot").float().clone()
+    torch.cuda.synchronize()
+    assert symm.watchdog_poll() is None
+    symm.set_watchdog_timeout_ms(300)
+    dist.barrier()
+    t0 = time.perf_counter()
+    if rank == 0:
+        pc.all_reduce(n, algo="oneshot")          # peers skip this epoch on purpose
+    else:
+        pc.epoch += 1
+    torch.cuda.synchronize()
+    waited = time.perf_counter() - t0
+    rec = symm.watchdog_poll()
+    if rank == 0:
+        assert rec is not None and rec["timed_out_waits"] >= 1 and rec["module"] == "collectives", rec
+        assert 0.25 < waited < 5.0, waited
+    else:
+        assert rec is None, rec
+    symm.set_watchdog_timeout_ms(30000)
+    dist.barrier()
+    # randomised launch skew: every rank delays its launch by a different amount each round
+    g = torch.Generator().manual_seed(1234 + rank)
+    for it in range(12):
+        pc.buf.tensor[:n].fill_(float(rank + 1))
+        torch.cuda.synchronize(); dist.barrier()
+        torch.cuda._sleep(int(torch.randint(0, 3_000_000, (1,), generator=g)))
+        got = pc.all_reduce(n, algo="oneshot").float()
+        assert torch.equal(got, ref), f"round {it}: all-reduce under launch skew differs"
+        torch.cuda.synchronize()
+    assert symm.watchdog_poll() is None
+    out["watchdog"] = {"first_record": rec, "waited_s": waited, "skew_rounds": 12}
+
+
+CASES = {"watchdog": case_watchdog, "probe": case_probe, "tp_kernels": case_tp_kernels, "zero_native": case_zero_native, "zero3_native": case_zero3_native,
          "tp_sp_engine": case_tp_sp_engine}
 
 

@@ -45,3 +45,8 @@ def test_tp_sp_engine_fused_matches_nccl(cuda_device):
 
 def test_zero3_peer_gather_matches_nccl(cuda_device):
     _run(["zero3_native"])
+
+
+def test_signal_watchdog_and_launch_skew(cuda_device):
+    out = _run(["watchdog"])
+    assert out["watchdog"]["skew_rounds"] == 12
