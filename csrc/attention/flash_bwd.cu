@@ -270,6 +270,11 @@ flash_bwd_dq_cast_kernel(const float* __restrict__ dq_acc, __nv_bfloat16* __rest
   }
 }
 
+int flash_bwd_v2_launch(const void* q, const void* k, const void* v, const void* o, const void* d_o, const float* lse,
+                        void* dq, void* dk, void* dv, float* scratch, int B, int S, int H, long long q_tok,
+                        long long k_tok, long long v_tok, long long o_tok, long long dqkv_tok, float scale, int causal,
+                        cudaStream_t s);
+
 }  // namespace llmctl
 
 using namespace llmctl;
@@ -287,6 +292,15 @@ LLMCTL_API int llmctl_flash_attn_bwd(const void* q, const void* k, const void* v
   LLMCTL_REQUIRE(q_tok_stride % 8 == 0 && k_tok_stride % 8 == 0 && v_tok_stride % 8 == 0 && o_tok_stride % 8 == 0 &&
                  dqkv_tok_stride % 8 == 0);
   cudaStream_t s = (cudaStream_t)stream;
+  static const int use_v1 = getenv("LLMCTL_FLASH_BWD_V1") ? 1 : 0;
+  if (!use_v1) {
+    // two deterministic kernels (dK/dV, then dQ), see flash_bwd2.cu; the single-kernel version below accumulates
+    // dQ with fp32 atomics and is kept for comparison
+    const int rc2 = flash_bwd_v2_launch(q, k, v, o, d_o, lse, dq, dk, dv, scratch, B, S, H, q_tok_stride, k_tok_stride,
+                                        v_tok_stride, o_tok_stride, dqkv_tok_stride, scale, causal, s);
+    if (rc2) LLMCTL_FAIL(rc2, "flash backward v2");
+    return 0;
+  }
   const long long n_tok = static_cast<long long>(B) * S;
   float* dq_acc = scratch;
   float* delta = scratch + n_tok * H * kBD;

@@ -257,6 +257,294 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
   }
 }
 
+
+// =====================================================================================================
+// Version 2: one CTA = one (batch, head, 256-query block) handled as two 128-query tiles A and B that share
+// every K/V tile (half the K/V smem traffic) and ping-pong on the tensor core: while the softmax warpgroup of
+// tile A works on S_A, the MMA warp runs P_B V / Q_B K^T and vice versa.
+//   warp 0      TMA producer (Q_A, Q_B once; K, V rings of 2 x 128 keys)
+//   warp 1      MMA issuer
+//   warps 2-5   softmax warpgroup of tile A      warps 6-9  softmax warpgroup of tile B
+// TMEM (all 512 columns): S_A [0,128) S_B [128,256) O_A [256,384) O_B [384,512).  P never touches shared
+// memory: the softmax thread overwrites the first 64 columns of its own S row with bf16x2 probabilities
+// (tcgen05.st) and P V reads its A operand straight from TMEM.  The tensor pipe executes in issue order, so
+// Q K^T of block j+1 (which overwrites S/P) is simply issued after P V of block j; tcgen05.commit covers every
+// earlier MMA, so "S(j+1) ready" also means "P V(j) has retired" and the O rescale needs no extra barrier.
+// The epilogue stages O through the (now idle) Q tile and writes it with TMA.
+constexpr int kF2Threads = 320;
+constexpr int kF2Smem = 6 * kTile + 1024;
+
+template <bool kDiag>
+__device__ __forceinline__ void softmax_block_v2(uint32_t tS, uint32_t tO, int row, bool first, float scale_log2,
+                                                 float& m_ref, float& l0, float& l1) {
+  // pass 1: raw row maximum (the scale is positive, so it commutes with max)
+  float bm = -INFINITY;
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    uint32_t r[64];
+    tmem_ld_x32(tS + h * 64, r);
+    tmem_ld_x32(tS + h * 64 + 32, r + 32);
+    tmem_ld_wait();
+    float m0 = -INFINITY, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
+#pragma unroll
+    for (int e = 0; e < 64; e += 4) {
+      float a = __uint_as_float(r[e]), b2 = __uint_as_float(r[e + 1]), c2 = __uint_as_float(r[e + 2]),
+            d2 = __uint_as_float(r[e + 3]);
+      if (kDiag) {
+        const int col = h * 64 + e;
+        if (col > row) a = -INFINITY;
+        if (col + 1 > row) b2 = -INFINITY;
+        if (col + 2 > row) c2 = -INFINITY;
+        if (col + 3 > row) d2 = -INFINITY;
+      }
+      m0 = fmaxf(m0, a);
+      m1 = fmaxf(m1, b2);
+      m2 = fmaxf(m2, c2);
+      m3 = fmaxf(m3, d2);
+    }
+    bm = fmaxf(bm, fmaxf(fmaxf(m0, m1), fmaxf(m2, m3)));
+  }
+  bm *= scale_log2;
+  // lazy reference update: only move the reference when the block maximum outgrows it by more than 2^8
+  const bool need = bm > m_ref + kRescaleThreshold;
+  float alpha = 1.f;
+  if (need) {
+    alpha = (m_ref == -INFINITY) ? 0.f : ex2_approx(m_ref - bm);
+    m_ref = bm;
+    l0 *= alpha;
+    l1 *= alpha;
+  }
+  if (!first && __any_sync(0xffffffffu, need)) {
+#pragma unroll 1
+    for (int c = 0; c < 4; ++c) {
+      uint32_t r[32];
+      tmem_ld_x32(tO + c * 32, r);
+      tmem_ld_wait();
+#pragma unroll
+      for (int e = 0; e < 32; e += 2) {
+        float x0, x1;
+        mul2(x0, x1, __uint_as_float(r[e]), __uint_as_float(r[e + 1]), alpha);
+        r[e] = __float_as_uint(x0);
+        r[e + 1] = __float_as_uint(x1);
+      }
+      tmem_st_x16(tO + c * 32, r);
+      tmem_st_x16(tO + c * 32 + 16, r + 16);
+    }
+    tmem_st_wait();
+  }
+  // pass 2: p = 2^(s*scale - m_ref) -> bf16x2 -> back into the first 64 columns of this S row
+  const float neg_m = -m_ref;
+  uint32_t r[2][32];
+  tmem_ld_x32(tS, r[0]);
+  tmem_ld_wait();
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    if (c + 1 < 4) tmem_ld_x32(tS + (c + 1) * 32, r[(c + 1) & 1]);   // in flight while chunk c is processed
+    uint32_t pk[16];
+#pragma unroll
+    for (int e = 0; e < 32; e += 2) {
+      float a0, a1;
+      fma2(a0, a1, __uint_as_float(r[c & 1][e]), __uint_as_float(r[c & 1][e + 1]), scale_log2, neg_m);
+      if (kDiag) {
+        if (c * 32 + e > row) a0 = -INFINITY;
+        if (c * 32 + e + 1 > row) a1 = -INFINITY;
+      }
+      const float p0 = ex2_approx(a0), p1 = ex2_approx(a1);
+      add2(l0, l1, p0, p1);
+      pk[e >> 1] = pack_bf16x2(p0, p1);
+    }
+    if (c + 1 < 4) tmem_ld_wait();        // chunk c+1 has landed (and chunk c was consumed) before P overwrites
+    tmem_st_x16(tS + c * 16, pk);
+  }
+  tmem_st_wait();
+}
+
+__global__ void __launch_bounds__(kF2Threads, 1)
+flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                  const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO,
+                  float* __restrict__ lse, int S, int H, float scale_log2, int causal) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint64_t bar_q[2], bar_kfull[2], bar_vfull[2], bar_kempty[2], bar_vempty[2];
+  __shared__ uint64_t bar_s[2], bar_p[2], bar_o[2];
+  __shared__ uint32_t tmem_base_smem;
+
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem = smem_raw + (smem_base - smem_u32(smem_raw));
+  // layout: Q_A, Q_B, K[2], V[2]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int qb2 = gridDim.x - 1 - blockIdx.x;          // heavy (late) query blocks first
+  const int head = blockIdx.y, b = blockIdx.z;
+  const int q0 = qb2 * 2 * kABM;
+  const bool validB = q0 + kABM < S;
+  const int nblk_t0 = causal ? (2 * qb2 + 1) : (S / kABN);
+  const int nblk_t1 = validB ? (causal ? (2 * qb2 + 2) : (S / kABN)) : 0;
+  const int nblk = nblk_t1 > nblk_t0 ? nblk_t1 : nblk_t0;
+  const int tok0 = b * S;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&bar_q[i], 1);
+      mbar_init(&bar_kfull[i], 1);
+      mbar_init(&bar_vfull[i], 1);
+      mbar_init(&bar_kempty[i], 1);
+      mbar_init(&bar_vempty[i], 1);
+      mbar_init(&bar_s[i], 1);
+      mbar_init(&bar_p[i], 4);
+      mbar_init(&bar_o[i], 1);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmQ);
+    prefetch_tmap(&tmK);
+    prefetch_tmap(&tmV);
+    prefetch_tmap(&tmO);
+  }
+  if (warp == 1) tmem_alloc<1>(&tmem_base_smem, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_smem;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_expect_tx(&bar_q[0], kTile);
+      tma_load_3d(smem, &tmQ, &bar_q[0], 0, head, tok0 + q0);
+      tma_load_3d(smem + kPanel, &tmQ, &bar_q[0], 64, head, tok0 + q0);
+      for (int j = 0; j < nblk; ++j) {
+        const int st = j & 1;
+        const uint32_t ph = (j >> 1) & 1u;
+        uint8_t* sK = smem + 2 * kTile + st * kTile;
+        uint8_t* sV = smem + 4 * kTile + st * kTile;
+        mbar_wait(&bar_kempty[st], ph ^ 1u);
+        mbar_expect_tx(&bar_kfull[st], kTile);
+        tma_load_3d(sK, &tmK, &bar_kfull[st], 0, head, tok0 + j * kABN);
+        tma_load_3d(sK + kPanel, &tmK, &bar_kfull[st], 64, head, tok0 + j * kABN);
+        if (j == 0 && validB) {        // Q_B right after the first K tile: tile A can start one load earlier
+          mbar_expect_tx(&bar_q[1], kTile);
+          tma_load_3d(smem + kTile, &tmQ, &bar_q[1], 0, head, tok0 + q0 + kABM);
+          tma_load_3d(smem + kTile + kPanel, &tmQ, &bar_q[1], 64, head, tok0 + q0 + kABM);
+        }
+        mbar_wait(&bar_vempty[st], ph ^ 1u);
+        mbar_expect_tx(&bar_vfull[st], kTile);
+        tma_load_3d(sV, &tmV, &bar_vfull[st], 0, head, tok0 + j * kABN);
+        tma_load_3d(sV + kPanel, &tmV, &bar_vfull[st], 64, head, tok0 + j * kABN);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc_qk = make_idesc_bf16(kABM, kABN, 0u, 0u);   // A, B K-major
+      constexpr uint32_t idesc_pv = make_idesc_bf16(kABM, kAD, 0u, 1u);    // A from TMEM, B MN-major (V)
+      auto nblk_of = [&](int t) { return t == 0 ? nblk_t0 : nblk_t1; };
+      auto issue_qk = [&](int t, int j, bool release_k) {
+        const int st = j & 1;
+        mbar_wait(&bar_kfull[st], (j >> 1) & 1u);
+        tc_fence_after();
+        const uint32_t q_addr = smem_base + t * kTile;
+        const uint32_t k_addr = smem_base + 2 * kTile + st * kTile;
+#pragma unroll
+        for (int ks = 0; ks < kAD / 16; ++ks) {
+          const uint32_t off = (ks >> 2) * kPanel + (ks & 3) * 32;
+          umma_ss<1>(tmem_base + t * 128, make_smem_desc(q_addr + off, 16, 1024, 2),
+                     make_smem_desc(k_addr + off, 16, 1024, 2), idesc_qk, ks != 0 ? 1u : 0u);
+        }
+        umma_commit<1>(&bar_s[t]);
+        if (release_k) umma_commit<1>(&bar_kempty[st]);
+      };
+      mbar_wait(&bar_q[0], 0);
+      issue_qk(0, 0, !validB);
+      if (validB) {
+        mbar_wait(&bar_q[1], 0);
+        issue_qk(1, 0, true);
+      }
+      for (int j = 0; j < nblk; ++j) {
+        const int st = j & 1;
+        for (int t = 0; t < 2; ++t) {
+          if (j >= nblk_of(t)) continue;
+          mbar_wait(&bar_vfull[st], (j >> 1) & 1u);
+          mbar_wait(&bar_p[t], j & 1u);                      // P_t(j) is in TMEM, O_t rescaled if needed
+          tc_fence_after();
+          const uint32_t v_addr = smem_base + 4 * kTile + st * kTile;
+          const uint32_t tP = tmem_base + t * 128;
+          const uint32_t tOt = tmem_base + 256 + t * 128;
+#pragma unroll
+          for (int ks = 0; ks < kABN / 16; ++ks)
+            umma_ts<1>(tOt, tP + ks * 8, make_smem_desc(v_addr + ks * 2048, kPanel, 1024, 2), idesc_pv,
+                       (j | ks) != 0 ? 1u : 0u);
+          if (t == 1 || j >= nblk_t1) umma_commit<1>(&bar_vempty[st]);    // last reader of V(j)
+          if (j + 1 < nblk_of(t))
+            issue_qk(t, j + 1, t == 1 || j + 1 >= nblk_t1);
+          else
+            umma_commit<1>(&bar_o[t]);
+        }
+      }
+    }
+  } else {
+    // ---------------------------- softmax warpgroups ----------------------------
+    const int t = (warp - 2) >> 2;
+    const int nb = t == 0 ? nblk_t0 : nblk_t1;
+    if (nb > 0) {
+      const int q = warp & 3;                        // TMEM lane quadrant this warp may touch
+      const int row = q * 32 + lane;
+      const int qt0 = q0 + t * kABM;
+      const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
+      const uint32_t tS = tmem_base + t * 128 + lane_off;
+      const uint32_t tOt = tmem_base + 256 + t * 128 + lane_off;
+      float m_ref = -INFINITY, l0 = 0.f, l1 = 0.f;
+      for (int j = 0; j < nb; ++j) {
+        mbar_wait(&bar_s[t], j & 1u);
+        tc_fence_after();
+        if (causal && j == nb - 1)
+          softmax_block_v2<true>(tS, tOt, row, j == 0, scale_log2, m_ref, l0, l1);
+        else
+          softmax_block_v2<false>(tS, tOt, row, j == 0, scale_log2, m_ref, l0, l1);
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bar_p[t]);
+      }
+      // ---- epilogue: O / l -> bf16 -> swizzled smem (the idle Q tile) -> TMA store; LSE ----
+      mbar_wait(&bar_o[t], 0);
+      tc_fence_after();
+      const float l = l0 + l1;
+      const float inv_l = 1.f / l;
+      uint8_t* stage = smem + t * kTile;
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        uint32_t r[32];
+        tmem_ld_x32(tOt + c * 32, r);
+        tmem_ld_wait();
+        uint8_t* prow = stage + (c >> 1) * kPanel + row * 128;
+#pragma unroll
+        for (int ch = 0; ch < 4; ++ch) {
+          uint32_t w[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e)
+            w[e] = pack_bf16x2(__uint_as_float(r[ch * 8 + 2 * e]) * inv_l, __uint_as_float(r[ch * 8 + 2 * e + 1]) * inv_l);
+          const int chunk = (c & 1) * 4 + ch;
+          *reinterpret_cast<uint4*>(prow + ((chunk ^ (row & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+        }
+      }
+      if (lse != nullptr)
+        lse[(static_cast<long long>(b) * H + head) * S + qt0 + row] = (m_ref + log2f(l)) * 0.6931471805599453f;
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        tma_store_3d(&tmO, stage + q * 32 * 128, 0, head, tok0 + qt0 + q * 32);
+        tma_store_3d(&tmO, stage + kPanel + q * 32 * 128, 64, head, tok0 + qt0 + q * 32);
+        tma_store_commit();
+        tma_store_wait_read<0>();
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<1>(tmem_base, 512);
+  }
+}
+
 }  // namespace llmctl
 
 using namespace llmctl;
@@ -278,6 +566,17 @@ LLMCTL_API int llmctl_flash_attn_fwd(const void* q, const void* k, const void* v
   if (rc) LLMCTL_FAIL(rc, "tensor map K");
   rc = get_tmap_3d_bf16(&tv, v, kAD, H, rows, kAD, v_tok_stride, 64, 1, kABN, 1);
   if (rc) LLMCTL_FAIL(rc, "tensor map V");
+  static const int use_v1 = getenv("LLMCTL_FLASH_FWD_V1") ? 1 : 0;
+  if (!use_v1 && scale > 0.f) {
+    CUtensorMap to;
+    rc = get_tmap_3d_bf16(&to, o, kAD, H, rows, kAD, o_tok_stride, 64, 1, 32, 1);
+    if (rc) LLMCTL_FAIL(rc, "tensor map O");
+    LLMCTL_CHECK(cudaFuncSetAttribute(flash_fwd2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kF2Smem));
+    dim3 grid2((S + 2 * kABM - 1) / (2 * kABM), H, B);
+    flash_fwd2_kernel<<<grid2, kF2Threads, kF2Smem, (cudaStream_t)stream>>>(tq, tk, tv, to, lse, S, H,
+                                                                          scale * 1.4426950408889634f, causal);
+    LLMCTL_RETURN_LAST();
+  }
   LLMCTL_CHECK(cudaFuncSetAttribute(flash_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttnSmem));
   dim3 grid(S / kABM, H, B);
   flash_fwd_kernel<<<grid, kAttnThreads, kAttnSmem, (cudaStream_t)stream>>>(

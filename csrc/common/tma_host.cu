@@ -61,7 +61,12 @@ static int encode_cached(CUtensorMap* out, const Key& key, int rank, const void*
   if (!fn) return static_cast<int>(cudaErrorNotSupported);
   // Driver entry points need a current context on *this* thread (autograd worker threads may not have
   // touched the runtime yet): a no-op runtime call binds the primary context.
-  (void)cudaFree(nullptr);
+  // Once per thread is enough, and keeps this path free of runtime calls while a CUDA graph is being captured.
+  static thread_local bool ctx_bound = false;
+  if (!ctx_bound) {
+    (void)cudaFree(nullptr);
+    ctx_bound = true;
+  }
   cuuint32_t estr[3] = {1, 1, 1};
   CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(base), dims,
                   strides_bytes, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,

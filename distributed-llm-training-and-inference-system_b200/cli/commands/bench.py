@@ -106,35 +106,51 @@ def e2e(
     qps: Optional[float] = typer.Option(None, "--qps", help="Request arrival rate (default: all at once)"),
     model: str = typer.Option("gpt-7b", "--model", help="Preset name or artifact directory"),
     num_requests: int = typer.Option(8, "--num-requests"), max_batch_size: int = typer.Option(8, "--max-batch-size"),
+    warmup_runs: int = typer.Option(1, "--warmup-runs", help="Untimed passes over the same workload first"),
+    cuda_graphs: bool = typer.Option(True, "--cuda-graphs/--no-cuda-graphs"),
     out: Optional[Path] = typer.Option(None, "--out"),
 ):
     """Serving benchmark: p50 TTFT and decode tokens/s (BASELINE.json config #5: 2k prompt / 256 decode)."""
     import torch
     from ...serve.engine import InferenceEngine
-    eng = InferenceEngine(model, max_batch_size=max_batch_size, max_batch_tokens=max(8192, max_batch_size * (prompt_length + gen_length)))
+    eng = InferenceEngine(model, max_batch_size=max_batch_size, max_batch_tokens=max(8192, max_batch_size * (prompt_length + gen_length)),
+                          cuda_graphs=cuda_graphs if torch.cuda.is_available() else False)
     V = eng.cfg.vocab_size
     g = torch.Generator().manual_seed(0)
     prompts = [torch.randint(3, min(V, 30000), (prompt_length,), generator=g).tolist() for _ in range(num_requests)]
     eos = getattr(eng.tokenizer, "eos_token_id", None)
     eng.tokenizer.eos_token_id = -1          # never stop early: fixed decode length
-    t0 = time.time(); seqs = []; nxt = 0
-    while nxt < num_requests or eng.has_work():
-        now = time.time() - t0
-        while nxt < num_requests and (qps is None or nxt / qps <= now):
-            seqs.append(eng.add_request(prompts[nxt], gen_length, temperature=0.0)); nxt += 1
-        if eng.has_work():
-            eng.step()
-        else:
-            time.sleep(0.001)
-    if torch.cuda.is_available():
-        torch.cuda.synchronize()
-    wall = time.time() - t0
+
+    def run_once():
+        for k in ("steps", "prefill_tokens", "decode_tokens", "preemptions", "prefill_time_s", "decode_time_s", "decode_steps"):
+            eng.stats[k] = 0
+        t0 = time.time(); seqs = []; nxt = 0
+        while nxt < num_requests or eng.has_work():
+            now = time.time() - t0
+            while nxt < num_requests and (qps is None or nxt / qps <= now):
+                seqs.append(eng.add_request(prompts[nxt], gen_length, temperature=0.0)); nxt += 1
+            if eng.has_work():
+                eng.step()
+            else:
+                time.sleep(0.001)
+        if torch.cuda.is_available():
+            torch.cuda.synchronize()
+        return seqs, time.time() - t0
+
+    for _ in range(warmup_runs):             # first pass pays lazy initialisation and CUDA-graph capture
+        run_once()
+    seqs, wall = run_once()
     eng.tokenizer.eos_token_id = eos
     ttft = sorted((s.first_token_time - s.created) for s in seqs if s.first_token_time)
     total_gen = sum(len(s.generated) for s in seqs)
+    st = eng.stats
     res = {"model": eng.cfg.name, "prompt_length": prompt_length, "gen_length": gen_length, "requests": num_requests,
            "ttft_p50_s": ttft[len(ttft) // 2] if ttft else None, "decode_tokens_per_s": total_gen / wall, "wall_s": wall,
-           "steps": eng.stats["steps"], "preemptions": eng.stats["preemptions"]}
+           "decode_only_tokens_per_s": st["decode_tokens"] / st["decode_time_s"] if st.get("decode_time_s") else None,
+           "decode_step_ms": 1e3 * st["decode_time_s"] / st["decode_steps"] if st.get("decode_steps") else None,
+           "prefill_tokens_per_s": st["prefill_tokens"] / st["prefill_time_s"] if st.get("prefill_time_s") else None,
+           "cuda_graphs": bool(getattr(eng, "cuda_graphs", False)),
+           "steps": st["steps"], "preemptions": st["preemptions"]}
     console.print_json(json.dumps(res))
     if out:
         Path(out).write_text(json.dumps(res, indent=2))

@@ -238,6 +238,49 @@ def load_model_weights(model: torch.nn.Module, ckpt: str | Path, strict: bool = 
                 p.copy_(sd[k].to(p.device, p.dtype))
 
 
+def reshard_optimizer_state(ckpt: str | Path, optimizer, saved_mesh: Dict[str, Any]) -> bool:
+    """Rebuild this rank's optimizer shard from a checkpoint written under a different DP degree / ZeRO stage
+    (same TP x PP partition, so the unit names and the parameter offsets inside each unit are unchanged; only the
+    tail padding and the [lo, hi) cut of every unit differ).  Returns False if a needed file or unit is missing."""
+    st = get_state()
+    ckpt = Path(ckpt)
+    tp, dp_old = int(saved_mesh.get("tp", 1)), int(saved_mesh.get("dp", 1))
+    if not hasattr(optimizer, "units"):
+        return False
+    files = [ckpt / "optim" / f"rank-{(st.pp_rank * dp_old + d) * tp + st.tp_rank:05d}.pt" for d in range(dp_old)]
+    if not all(f.exists() for f in files):
+        return False
+    shards = [torch.load(f, map_location="cpu", weights_only=False) for f in files]
+    for u in optimizer.units:
+        pieces = []
+        for sd in shards:
+            s = sd["units"].get(u.name)
+            if s is None:
+                return False
+            pieces.append(s)
+            if s["lo"] == 0 and s["hi"] >= s["numel"]:       # replicated state (ZeRO-0): one copy is enough
+                break
+        lo, hi = u.state_lo, u.state_hi
+        for key, dst in (("master", u.master), ("exp_avg", u.exp_avg), ("exp_avg_sq", u.exp_avg_sq)):
+            dst.zero_()                                       # anything not covered below is tail padding
+            for s in pieces:
+                a, b = max(lo, int(s["lo"])), min(hi, int(s["hi"]))
+                if a < b:
+                    dst[a - lo:b - lo].copy_(s[key][a - int(s["lo"]):b - int(s["lo"])])
+        covered = sorted((max(lo, int(s["lo"])), min(hi, int(s["hi"]))) for s in pieces)
+        reach = lo
+        for a, b in covered:
+            if a > reach:
+                break
+            reach = max(reach, b)
+        real_end = u.offsets[-1] + u.shapes[-1].numel() if u.offsets else 0
+        if reach < min(hi, real_end):
+            return False                                      # a hole over real parameters: do not guess
+        optimizer._publish(u)
+    optimizer.step_count = int(shards[0]["step"])
+    return True
+
+
 def load_checkpoint(ckpt: str | Path, model: torch.nn.Module, optimizer=None, *, restore_rng: bool = True,
                     strict: bool = True) -> Dict[str, Any]:
     """Full resume: weights, optimizer shard (fp32 master re-published into the parameters), RNG; returns
@@ -269,6 +312,10 @@ def load_checkpoint(ckpt: str | Path, model: torch.nn.Module, optimizer=None, *,
     if optimizer is not None:
         if same_mesh and opt_file.exists() and mesh.get("zero_stage", 0) == getattr(optimizer, "zero_stage", 0):
             optimizer.load_state_dict(torch.load(opt_file, map_location=st.device, weights_only=False))
+        elif (mesh.get("tp", 1), mesh.get("pp", 1)) == (st.tp, st.pp) and reshard_optimizer_state(ckpt, optimizer, mesh):
+            # same model partition, different data-parallel degree and/or ZeRO stage: the saved fp32 master
+            # weights and Adam moments were re-cut to this rank's slice of every unit
+            tstate["optimizer_resharded"] = True
         else:
             # plan changed: rebuild fp32 master weights from the (re-sharded) parameters, reset the moments
             if hasattr(optimizer, "reset_from_params"):

@@ -33,8 +33,12 @@ def kv_append(qkv: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, s
 
 
 def choose_splits(batch: int, heads: int, max_context: int, block_size: int, sms: int = 148) -> int:
-    want = max(1, (4 * sms + batch * heads - 1) // (batch * heads))          # ~4 CTAs per SM keeps HBM busy
-    return int(max(1, min(want, max(1, max_context // max(4 * block_size, 64)), 64)))
+    # Decode attention is a latency-bound stream: each CTA walks block table -> K/V rows -> online softmax in a
+    # dependent chain, so HBM only fills up with ~8 resident CTAs per SM.  Splits are whole KV blocks of >= 64 tokens;
+    # the merge pass costs (head_dim + 2) floats per split, ~3 % of the K/V bytes at 64 tokens per split.
+    want = max(1, (8 * sms + batch * heads - 1) // (batch * heads))
+    per_split = max(block_size, (64 // block_size) * block_size) if block_size <= 64 else block_size
+    return int(max(1, min(want, max(1, max_context // per_split), 256)))
 
 
 def paged_attention_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,

@@ -20,6 +20,7 @@ from dataclasses import dataclass, field
 from pathlib import Path
 from typing import Dict, List, Optional, Tuple
 
+import numpy as np
 import torch
 import torch.nn.functional as F
 
@@ -85,10 +86,74 @@ class Sequence:
         return self.prompt_ids + self.generated
 
 
+class _HostViews:
+    """numpy views into one pinned staging buffer."""
+
+    def __init__(self, buf: torch.Tensor, B: int, max_blocks: int):
+        a = buf.numpy()
+        self.tokens = a[0:2 * B].view(np.int64)
+        self.slots = a[2 * B:4 * B].view(np.int64)
+        self.positions = a[4 * B:5 * B]
+        self.ctx = a[5 * B:6 * B]
+        self.block_tables = a[6 * B:6 * B + B * max_blocks].reshape(B, max_blocks)
+
+    def fill_pad(self) -> None:
+        # padded rows: token 0 at position 0, empty context, no cache slot (K13 skips slot -1)
+        self.tokens[:] = 0
+        self.slots[:] = -1
+        self.positions[:] = 0
+        self.ctx[:] = 0
+        self.block_tables[:] = 0
+
+
+class _DecodeInputs:
+    """Static device inputs of a decode step of (padded) batch ``B`` and ``max_blocks`` table columns, laid out in
+    one int32 buffer: tokens(int64) | slots(int64) | positions | context lengths | block tables."""
+
+    def __init__(self, B: int, max_blocks: int, device: torch.device):
+        n = 6 * B + B * max_blocks
+        pin = device.type == "cuda"
+        self._hbuf = torch.zeros(n, dtype=torch.int32, pin_memory=pin)
+        self._dbuf = torch.zeros(n, dtype=torch.int32, device=device)
+        self.host = _HostViews(self._hbuf, B, max_blocks)
+        d = self._dbuf
+        self.tokens = d[0:2 * B].view(torch.int64).view(B, 1)
+        self.slots = d[2 * B:4 * B].view(torch.int64)
+        self.positions = d[4 * B:5 * B]
+        self.ctx = d[5 * B:6 * B]
+        self.block_tables = d[6 * B:].view(B, max_blocks)
+        self.nbytes = n * 4
+
+    def upload(self) -> None:
+        self._dbuf.copy_(self._hbuf, non_blocking=True)
+
+
+class _DecodeGraph:
+    """One captured decode step.  Inputs are the static views of ``_DecodeInputs``; the logits land in a static
+    output tensor owned by the graph's memory pool."""
+
+    def __init__(self, engine: "InferenceEngine", inp: _DecodeInputs, B: int, max_ctx: int):
+        side = torch.cuda.Stream(device=engine.device)
+        side.wait_stream(torch.cuda.current_stream(engine.device))
+        with torch.cuda.stream(side):
+            for _ in range(2):                              # warm-up: tensor-map cache, lazy inits, cuBLAS handles
+                engine._decode_core(inp, B, max_ctx)
+        torch.cuda.current_stream(engine.device).wait_stream(side)
+        torch.cuda.synchronize(engine.device)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph, capture_error_mode="thread_local"):
+            self.logits = engine._decode_core(inp, B, max_ctx)
+
+    def replay(self) -> torch.Tensor:
+        self.graph.replay()
+        return self.logits
+
+
 class InferenceEngine:
     def __init__(self, artifact: str | Path, *, max_batch_size: int = 8, max_batch_tokens: int = 8192,
                  scheduler: str = "dynamic", device: Optional[str] = None, kv_block_size: int = 16,
-                 kv_memory_fraction: float = 0.5, num_kv_blocks: Optional[int] = None, seed: int = 0):
+                 kv_memory_fraction: float = 0.5, num_kv_blocks: Optional[int] = None, seed: int = 0,
+                 cuda_graphs: Optional[bool] = None):
         self.model, self.cfg, self.tokenizer, self.device = load_model_for_inference(artifact, device)
         self.st = get_state()
         m = self.model
@@ -116,8 +181,17 @@ class InferenceEngine:
         self.gen = torch.Generator(device=self.device)
         self.gen.manual_seed(seed)
         self.max_context = min(self.cfg.max_position_embeddings, max_batch_tokens)
-        self.stats = {"steps": 0, "prefill_tokens": 0, "decode_tokens": 0, "preemptions": 0}
+        self.stats = {"steps": 0, "prefill_tokens": 0, "decode_tokens": 0, "preemptions": 0, "prefill_time_s": 0.0,
+                      "decode_time_s": 0.0, "decode_steps": 0}
         self._scratch = None
+        # decode runs as a replayed CUDA graph per (batch bucket, context bucket): the step is launch-bound
+        # (~10 small kernels per layer), so replay removes the per-kernel Python + launch cost.  TP ranks keep the
+        # eager path (the peer-signal epochs of the fused all-reduce are launch arguments, not graph-replayable).
+        if cuda_graphs is None:
+            cuda_graphs = self.device.type == "cuda" and self.st.tp == 1
+        self.cuda_graphs = bool(cuda_graphs) and self.device.type == "cuda"
+        self._graphs: Dict[Tuple[int, int], "_DecodeGraph"] = {}
+        self._staging: Dict[Tuple[int, int], "_DecodeInputs"] = {}
 
     # ---- request API ---------------------------------------------------------------------------------
     def add_request(self, prompt_ids: List[int], max_tokens: int = 100, temperature: float = 1.0, top_p: float = 1.0,
@@ -186,39 +260,72 @@ class InferenceEngine:
         self.stats["prefill_tokens"] += n
         return logits[0]
 
-    @torch.no_grad()
-    def _decode(self, seqs: List[Sequence]) -> torch.Tensor:
-        """One token for every sequence in ``seqs``; returns logits [B, V]."""
-        B = len(seqs)
+    def _decode_core(self, inp: "_DecodeInputs", B: int, max_ctx: int) -> torch.Tensor:
+        """Device-only part of a decode step over the static input views (capturable in a CUDA graph)."""
         H, D = self.heads_local, self.head_dim
-        last = [s.all_ids[-1] for s in seqs]
-        ctx = [len(s.all_ids) for s in seqs]               # context length including the token being processed
-        tokens = torch.tensor(last, dtype=torch.int64, device=self.device).view(B, 1)
-        positions = torch.tensor([c - 1 for c in ctx], dtype=torch.int32, device=self.device)
-        tables = [self.kv.block_table(s.req_id) for s in seqs]
-        max_blocks = max(len(t) for t in tables)
-        bt = torch.zeros(B, max_blocks, dtype=torch.int32)
-        for r, t in enumerate(tables):
-            bt[r, :len(t)] = torch.tensor(t, dtype=torch.int32)
-        bt = bt.to(self.device)
-        ctx_t = torch.tensor(ctx, dtype=torch.int32, device=self.device)
-        slots = torch.stack([self._slots(s.req_id, c - 1, 1)[0] for s, c in zip(seqs, ctx)])
-        max_ctx = max(ctx)
         m = self.model
 
         def attn(i, qkv):
-            sops.kv_append(qkv, self.k_caches[i], self.v_caches[i], slots, H, D)
+            sops.kv_append(qkv, self.k_caches[i], self.v_caches[i], inp.slots, H, D)
             q = qkv[:, :H * D].reshape(B, H, D)
-            o = sops.paged_attention_decode(q, self.k_caches[i], self.v_caches[i], bt, ctx_t, max_ctx)
+            o = sops.paged_attention_decode(q, self.k_caches[i], self.v_caches[i], inp.block_tables, inp.ctx, max_ctx)
             return o.reshape(B, H * D)
 
-        x, residual = m.embed_tokens(tokens), None
+        x, residual = m.embed_tokens(inp.tokens), None
         for i, blk in enumerate(m.blocks):
-            x, residual = self._layer(i, blk, x, residual, positions, attn)
+            x, residual = self._layer(i, blk, x, residual, inp.positions, attn)
         y, _ = m.final_norm(x, residual)
-        logits = m.lm_head(y) if m.lm_head is not None else ops.linear(y, m.embed.weight)
+        return m.lm_head(y) if m.lm_head is not None else ops.linear(y, m.embed.weight)
+
+    @staticmethod
+    def _bucket(n: int, lo: int, hi: int) -> int:
+        b = lo
+        while b < n:
+            b *= 2
+        return min(b, max(hi, n))
+
+    @torch.no_grad()
+    def _decode(self, seqs: List[Sequence]) -> torch.Tensor:
+        """One token for every sequence in ``seqs``; returns logits [B, V].  The step's inputs (last tokens,
+        positions, context lengths, cache slots, block tables) are packed into one pinned host buffer and reach
+        the device in a single copy."""
+        B = len(seqs)
+        ctx = [len(s.all_ids) for s in seqs]               # context length including the token being processed
+        max_ctx = max(ctx)
+        if self.cuda_graphs:
+            Bb = self._bucket(B, 1, self.sched_max_batch())
+            cb = self._bucket(max_ctx, 256, max(self.max_context, max_ctx))
+        else:
+            Bb, cb = B, max_ctx
+        max_blocks = (cb + self.block_size - 1) // self.block_size
+        key = (Bb, max_blocks)
+        inp = self._staging.get(key)
+        if inp is None:
+            if len(self._staging) > 64:
+                self._staging.clear()
+                self._graphs.clear()
+            inp = self._staging[key] = _DecodeInputs(Bb, max_blocks, self.device)
+        h = inp.host
+        h.fill_pad()
+        bs = self.block_size
+        for r, (s, c) in enumerate(zip(seqs, ctx)):
+            table = self.kv.block_table(s.req_id)
+            h.tokens[r] = s.all_ids[-1]
+            h.positions[r] = c - 1
+            h.ctx[r] = c
+            h.slots[r] = table[(c - 1) // bs] * bs + (c - 1) % bs
+            h.block_tables[r, :len(table)] = table
+        inp.upload()
         self.stats["decode_tokens"] += B
-        return logits
+        if not self.cuda_graphs:
+            return self._decode_core(inp, Bb, cb)[:B]
+        g = self._graphs.get(key)
+        if g is None:
+            g = self._graphs[key] = _DecodeGraph(self, inp, Bb, cb)
+        return g.replay()[:B]
+
+    def sched_max_batch(self) -> int:
+        return max(int(getattr(self.sched, "max_batch_size", 8)), 1)
 
     def _gather_vocab(self, logits: torch.Tensor) -> torch.Tensor:
         """TP: logits are vocab shards; gather to the full vocabulary (tiny [B, V] all-gather)."""
@@ -254,15 +361,21 @@ class InferenceEngine:
         self.stats["steps"] += 1
         finished: List[Sequence] = []
         decode = [self.seqs[r] for r, ph, _ in plan if ph == DECODE]
+        # the sampled ids are read back in every phase (the step's only sync), so host clocks bracket device work
+        t0 = time.perf_counter()
         for r, ph, _ in plan:
             if ph == PREFILL:
                 s = self.seqs[r]
                 tok = self._sample(self._prefill(s), [s])[0]
                 self._emit(s, tok, finished)
+        t1 = time.perf_counter()
+        self.stats["prefill_time_s"] += t1 - t0
         if decode:
             toks = self._sample(self._decode(decode), decode)
             for s, tok in zip(decode, toks):
                 self._emit(s, tok, finished)
+            self.stats["decode_time_s"] += time.perf_counter() - t1
+            self.stats["decode_steps"] += 1
         pre = self.sched.pop_preempted()
         self.stats["preemptions"] += len(pre)
         return finished

@@ -1,0 +1,16 @@
+#!/bin/bash
+mkdir -p gpurun_out; rm -f gpurun_out/rc.txt
+LLMCTL_DEBUG=1 timeout 300 python -m pytest tests/test_kernels_gpu.py -m gpu -q -k "flash" --timeout 60 --timeout-method=thread > gpurun_out/t_flash.log 2>&1; echo "flash rc=$?" >> gpurun_out/rc.txt
+LLMCTL_DEBUG=1 timeout 300 python -m pytest tests/test_serving_gpu.py -m gpu -q --timeout 120 --timeout-method=thread > gpurun_out/t_serving.log 2>&1; echo "serving rc=$?" >> gpurun_out/rc.txt
+timeout 300 python tools/bench_attention.py --out gpurun_out/attention_v2.json > gpurun_out/attn_v2.log 2>&1; echo "attn_v2 rc=$?" >> gpurun_out/rc.txt
+timeout 600 python bin/llmctl bench e2e --gen-length 128 --out gpurun_out/bench_e2e_graph.json > gpurun_out/bench_e2e_graph.log 2>&1; echo "e2e rc=$?" >> gpurun_out/rc.txt
+cat gpurun_out/rc.txt; tail -n 15 gpurun_out/t_flash.log | cut -c1-300; tail -n 8 gpurun_out/t_serving.log | cut -c1-300
+python - <<'PY'
+import json
+for f in ("gpurun_out/attention_v2.json",):
+    try:
+        for r in json.load(open(f)):
+            print(r["shape"], "native fwd %.3f (%.0f TF) f+b %.3f | cudnn fwd %.3f f+b %.3f | x%.2f x%.2f" % (r["native"]["fwd_ms"], r["native"]["fwd_tflops"], r["native"]["fwd_bwd_ms"], r["cudnn"]["fwd_ms"], r["cudnn"]["fwd_bwd_ms"], r["fwd_speedup_vs_cudnn"], r["fwd_bwd_speedup_vs_cudnn"]))
+    except Exception as e: print(f, e)
+PY
+tail -n 12 gpurun_out/bench_e2e_graph.log | cut -c1-300
