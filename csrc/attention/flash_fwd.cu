@@ -262,49 +262,49 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
 // Version 2: one CTA = one (batch, head, 256-query block) handled as two 128-query tiles A and B that share
 // every K/V tile (half the K/V smem traffic) and ping-pong on the tensor core: while the softmax warpgroup of
 // tile A works on S_A, the MMA warp runs P_B V / Q_B K^T and vice versa.
-//   warp 0      TMA producer (Q_A, Q_B once; K, V rings of 2 x 128 keys)
-//   warp 1      MMA issuer
-//   warps 2-5   softmax warpgroup of tile A      warps 6-9  softmax warpgroup of tile B
+//   warps 0-3   softmax warpgroup of tile A      warps 4-7  softmax warpgroup of tile B
+//   warp 8      TMA producer (Q_A, Q_B once; K, V rings of 2 x 128 keys)
+//   warp 9      MMA issuer                       warps 10-11 idle (they complete the third warpgroup so that
+//               setmaxnreg can move its registers to the softmax warpgroups: 216 per softmax thread, enough to
+//               hold a whole 128-column S row plus the packed P chunk without spilling)
 // TMEM (all 512 columns): S_A [0,128) S_B [128,256) O_A [256,384) O_B [384,512).  P never touches shared
 // memory: the softmax thread overwrites the first 64 columns of its own S row with bf16x2 probabilities
 // (tcgen05.st) and P V reads its A operand straight from TMEM.  The tensor pipe executes in issue order, so
 // Q K^T of block j+1 (which overwrites S/P) is simply issued after P V of block j; tcgen05.commit covers every
 // earlier MMA, so "S(j+1) ready" also means "P V(j) has retired" and the O rescale needs no extra barrier.
 // The epilogue stages O through the (now idle) Q tile and writes it with TMA.
-constexpr int kF2Threads = 320;
+constexpr int kF2Threads = 384;
 constexpr int kF2Smem = 6 * kTile + 1024;
 
 template <bool kDiag>
 __device__ __forceinline__ void softmax_block_v2(uint32_t tS, uint32_t tO, int row, bool first, float scale_log2,
                                                  float& m_ref, float& l0, float& l1) {
+  // The whole S row (128 fp32) is read from TMEM once and stays in registers for both passes: every
+  // tcgen05.ld -> wait round trip removed here is latency the tensor pipe would otherwise sit idle for.
+  uint32_t r[128];
+  tmem_ld_x32(tS, r);
+  tmem_ld_x32(tS + 32, r + 32);
+  tmem_ld_x32(tS + 64, r + 64);
+  tmem_ld_x32(tS + 96, r + 96);
+  tmem_ld_wait();
   // pass 1: raw row maximum (the scale is positive, so it commutes with max)
-  float bm = -INFINITY;
+  float m0 = -INFINITY, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
 #pragma unroll
-  for (int h = 0; h < 2; ++h) {
-    uint32_t r[64];
-    tmem_ld_x32(tS + h * 64, r);
-    tmem_ld_x32(tS + h * 64 + 32, r + 32);
-    tmem_ld_wait();
-    float m0 = -INFINITY, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
-#pragma unroll
-    for (int e = 0; e < 64; e += 4) {
-      float a = __uint_as_float(r[e]), b2 = __uint_as_float(r[e + 1]), c2 = __uint_as_float(r[e + 2]),
-            d2 = __uint_as_float(r[e + 3]);
-      if (kDiag) {
-        const int col = h * 64 + e;
-        if (col > row) a = -INFINITY;
-        if (col + 1 > row) b2 = -INFINITY;
-        if (col + 2 > row) c2 = -INFINITY;
-        if (col + 3 > row) d2 = -INFINITY;
-      }
-      m0 = fmaxf(m0, a);
-      m1 = fmaxf(m1, b2);
-      m2 = fmaxf(m2, c2);
-      m3 = fmaxf(m3, d2);
+  for (int e = 0; e < 128; e += 4) {
+    float a = __uint_as_float(r[e]), b2 = __uint_as_float(r[e + 1]), c2 = __uint_as_float(r[e + 2]),
+          d2 = __uint_as_float(r[e + 3]);
+    if (kDiag) {
+      if (e > row) a = -INFINITY;
+      if (e + 1 > row) b2 = -INFINITY;
+      if (e + 2 > row) c2 = -INFINITY;
+      if (e + 3 > row) d2 = -INFINITY;
     }
-    bm = fmaxf(bm, fmaxf(fmaxf(m0, m1), fmaxf(m2, m3)));
+    m0 = fmaxf(m0, a);
+    m1 = fmaxf(m1, b2);
+    m2 = fmaxf(m2, c2);
+    m3 = fmaxf(m3, d2);
   }
-  bm *= scale_log2;
+  const float bm = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3)) * scale_log2;
   // lazy reference update: only move the reference when the block maximum outgrows it by more than 2^8
   const bool need = bm > m_ref + kRescaleThreshold;
   float alpha = 1.f;
@@ -314,37 +314,16 @@ __device__ __forceinline__ void softmax_block_v2(uint32_t tS, uint32_t tO, int r
     l0 *= alpha;
     l1 *= alpha;
   }
-  if (!first && __any_sync(0xffffffffu, need)) {
-#pragma unroll 1
-    for (int c = 0; c < 4; ++c) {
-      uint32_t r[32];
-      tmem_ld_x32(tO + c * 32, r);
-      tmem_ld_wait();
-#pragma unroll
-      for (int e = 0; e < 32; e += 2) {
-        float x0, x1;
-        mul2(x0, x1, __uint_as_float(r[e]), __uint_as_float(r[e + 1]), alpha);
-        r[e] = __float_as_uint(x0);
-        r[e + 1] = __float_as_uint(x1);
-      }
-      tmem_st_x16(tO + c * 32, r);
-      tmem_st_x16(tO + c * 32 + 16, r + 16);
-    }
-    tmem_st_wait();
-  }
+  const bool rescale = !first && __any_sync(0xffffffffu, need);
   // pass 2: p = 2^(s*scale - m_ref) -> bf16x2 -> back into the first 64 columns of this S row
   const float neg_m = -m_ref;
-  uint32_t r[2][32];
-  tmem_ld_x32(tS, r[0]);
-  tmem_ld_wait();
 #pragma unroll
   for (int c = 0; c < 4; ++c) {
-    if (c + 1 < 4) tmem_ld_x32(tS + (c + 1) * 32, r[(c + 1) & 1]);   // in flight while chunk c is processed
     uint32_t pk[16];
 #pragma unroll
     for (int e = 0; e < 32; e += 2) {
       float a0, a1;
-      fma2(a0, a1, __uint_as_float(r[c & 1][e]), __uint_as_float(r[c & 1][e + 1]), scale_log2, neg_m);
+      fma2(a0, a1, __uint_as_float(r[c * 32 + e]), __uint_as_float(r[c * 32 + e + 1]), scale_log2, neg_m);
       if (kDiag) {
         if (c * 32 + e > row) a0 = -INFINITY;
         if (c * 32 + e + 1 > row) a1 = -INFINITY;
@@ -353,8 +332,25 @@ __device__ __forceinline__ void softmax_block_v2(uint32_t tS, uint32_t tO, int r
       add2(l0, l1, p0, p1);
       pk[e >> 1] = pack_bf16x2(p0, p1);
     }
-    if (c + 1 < 4) tmem_ld_wait();        // chunk c+1 has landed (and chunk c was consumed) before P overwrites
     tmem_st_x16(tS + c * 16, pk);
+  }
+  if (rescale) {
+    // rare (reference moved by more than 2^8): scale the running O row; P stores above are already in flight
+#pragma unroll 1
+    for (int c = 0; c < 4; ++c) {
+      uint32_t o[32];
+      tmem_ld_x32(tO + c * 32, o);
+      tmem_ld_wait();
+#pragma unroll
+      for (int e = 0; e < 32; e += 2) {
+        float x0, x1;
+        mul2(x0, x1, __uint_as_float(o[e]), __uint_as_float(o[e + 1]), alpha);
+        o[e] = __float_as_uint(x0);
+        o[e + 1] = __float_as_uint(x1);
+      }
+      tmem_st_x16(tO + c * 32, o);
+      tmem_st_x16(tO + c * 32 + 16, o + 16);
+    }
   }
   tmem_st_wait();
 }
@@ -394,19 +390,20 @@ flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
     }
     fence_mbar_init();
   }
-  if (warp == 0 && lane == 0) {
+  if (warp == 8 && lane == 0) {
     prefetch_tmap(&tmQ);
     prefetch_tmap(&tmK);
     prefetch_tmap(&tmV);
     prefetch_tmap(&tmO);
   }
-  if (warp == 1) tmem_alloc<1>(&tmem_base_smem, 512);
+  if (warp == 9) tmem_alloc<1>(&tmem_base_smem, 512);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_smem;
-
-  if (warp == 0) {
+  if (warp >= 8) {
+   setmaxnreg_dec<72>();
+   if (warp == 8) {
     if (lane == 0) {
       mbar_expect_tx(&bar_q[0], kTile);
       tma_load_3d(smem, &tmQ, &bar_q[0], 0, head, tok0 + q0);
@@ -431,7 +428,7 @@ flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
         tma_load_3d(sV + kPanel, &tmV, &bar_vfull[st], 64, head, tok0 + j * kABN);
       }
     }
-  } else if (warp == 1) {
+  } else if (warp == 9) {
     if (lane == 0) {
       constexpr uint32_t idesc_qk = make_idesc_bf16(kABM, kABN, 0u, 0u);   // A, B K-major
       constexpr uint32_t idesc_pv = make_idesc_bf16(kABM, kAD, 0u, 1u);    // A from TMEM, B MN-major (V)
@@ -479,9 +476,11 @@ flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
         }
       }
     }
+   }
   } else {
+    setmaxnreg_inc<216>();
     // ---------------------------- softmax warpgroups ----------------------------
-    const int t = (warp - 2) >> 2;
+    const int t = warp >> 2;
     const int nb = t == 0 ? nblk_t0 : nblk_t1;
     if (nb > 0) {
       const int q = warp & 3;                        // TMEM lane quadrant this warp may touch
@@ -539,7 +538,7 @@ flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) {
+  if (warp == 9) {
     tc_fence_after();
     tmem_dealloc<1>(tmem_base, 512);
   }

@@ -272,7 +272,53 @@ def case_watchdog(out):
     out["watchdog"] = {"first_record": rec, "waited_s": waited, "skew_rounds": 12}
 
 
-CASES = {"watchdog": case_watchdog, "probe": case_probe, "tp_kernels": case_tp_kernels, "zero_native": case_zero_native, "zero3_native": case_zero3_native,
+def case_tp_serving(out):
+    """Tensor-parallel decode: K11 (fused all-reduce + residual + RMSNorm) vs NCCL all-reduce + ATen, same engine."""
+    import time
+    from llmctl_b200.comms import mesh
+    from llmctl_b200.models.config import ModelConfig
+    from llmctl_b200.serve import engine as E
+    world = dist.get_world_size()
+    mesh.reset_state()
+    mesh.init_mesh(tp=world)
+    torch.manual_seed(1234 + dist.get_rank())
+    cfg = ModelConfig(name="serve-tp", layers=4, hidden=1024, ffn=2816, heads=8, vocab_size=4096, max_position_embeddings=1024)
+    orig = E.resolve_model
+    E.resolve_model = lambda spec: cfg
+    try:
+        eng = E.InferenceEngine("serve-tp", max_batch_size=8, max_batch_tokens=8192, num_kv_blocks=512)
+    finally:
+        E.resolve_model = orig
+    assert eng._ar is not None, "fused TP decode context was not created"
+    g = torch.Generator().manual_seed(7)
+    prompts = [torch.randint(3, 4000, (n,), generator=g).tolist() for n in (33, 64, 17, 128, 50, 77, 90, 12)]
+    res = {}
+    ar = eng._ar
+    toks = {}
+    for mode in ("fused", "nccl", "fused"):
+        eng._ar = ar if mode == "fused" else None
+        torch.cuda.synchronize(); dist.barrier()
+        t0 = time.perf_counter()
+        toks[mode] = eng.generate(prompts, max_tokens=24, temperature=0.0)
+        torch.cuda.synchronize()
+        res[mode + "_s"] = time.perf_counter() - t0
+        res[mode + "_decode_step_ms"] = 1e3 * eng.stats["decode_time_s"] / max(eng.stats["decode_steps"], 1)
+        eng.stats["decode_time_s"], eng.stats["decode_steps"] = 0.0, 0
+    agree = sum(int(a == b) for x, y in zip(toks["fused"], toks["nccl"]) for a, b in zip(x, y))
+    total = sum(len(x) for x in toks["fused"])
+    first = sum(int(x[0] == y[0]) for x, y in zip(toks["fused"], toks["nccl"]))
+    res.update(agree=agree, total=total, first_token_agree=first)
+    # all TP ranks must have produced the same tokens
+    mine = torch.tensor([t for x in toks["fused"] for t in x], device="cuda")
+    ref = mine.clone(); dist.broadcast(ref, src=0)
+    assert torch.equal(mine, ref), "TP ranks diverged"
+    assert first == len(prompts) and agree >= 0.8 * total, res
+    from llmctl_b200.comms import symm
+    assert symm.watchdog_poll() is None
+    out["tp_serving"] = res
+
+
+CASES = {"tp_serving": case_tp_serving, "watchdog": case_watchdog, "probe": case_probe, "tp_kernels": case_tp_kernels, "zero_native": case_zero_native, "zero3_native": case_zero3_native,
          "tp_sp_engine": case_tp_sp_engine}
 
 

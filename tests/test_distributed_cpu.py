@@ -112,3 +112,35 @@ def test_pp2_checkpoint_resume(tmp_path):
     import json
     rows = [json.loads(l) for l in open(tmp_path / "metrics.jsonl")] if (tmp_path / "metrics.jsonl").exists() else []
     assert res[0] == pytest.approx(res[1])
+
+
+def _zero1_save_worker(rank, world, out_dir):
+    eng = _make_engine(out_dir, zero_stage=1, batch_size=2, max_steps=2, save_steps=2)
+    eng.prepare_datasets()
+    eng.setup_optimizer_and_scheduler()
+    eng.train()
+    return True
+
+
+def test_optimizer_state_resharded_when_dp_changes(tmp_path):
+    """A checkpoint written by dp=2 / ZeRO-1 resumes on one process with the Adam state intact (re-cut, not reset)."""
+    from llmctl_b200.comms import mesh
+    run_distributed(_zero1_save_worker, 2, str(tmp_path))
+    ck = tmp_path / "final"
+    shards = [torch.load(ck / "optim" / f"rank-{r:05d}.pt", weights_only=False) for r in range(2)]
+    mesh.reset_state()
+    eng = _make_engine(str(tmp_path / "resumed"), zero_stage=0, batch_size=4, max_steps=3)
+    eng.prepare_datasets()
+    eng.setup_optimizer_and_scheduler()
+    eng.load_checkpoint(str(ck))
+    assert eng.global_step == 2 and eng.optimizer.step_count == 2
+    for u in eng.optimizer.units:
+        old = [s["units"][u.name] for s in shards]
+        for key, mine in (("master", u.master), ("exp_avg", u.exp_avg), ("exp_avg_sq", u.exp_avg_sq)):
+            full = torch.cat([o[key] for o in old])
+            n = min(full.numel(), mine.numel())
+            assert torch.equal(mine[:n].cpu(), full[:n]), f"{u.name}.{key} differs after re-sharding"
+        assert float(u.exp_avg.abs().sum()) > 0
+    out = eng.train_step()
+    assert torch.isfinite(out["loss"]).all()
+    mesh.reset_state()

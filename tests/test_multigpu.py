@@ -50,3 +50,8 @@ def test_zero3_peer_gather_matches_nccl(cuda_device):
 def test_signal_watchdog_and_launch_skew(cuda_device):
     out = _run(["watchdog"])
     assert out["watchdog"]["skew_rounds"] == 12
+
+
+def test_tp_serving_fused_allreduce_norm(cuda_device):
+    out = _run(["tp_serving"])
+    assert out["tp_serving"]["first_token_agree"] == 8
