@@ -37,7 +37,7 @@ kv_append_kernel(const __nv_bfloat16* __restrict__ qkv, long long row_stride, in
 }
 
 // ---------------------------------------------------------------------------------------------
-// K12: decode attention.  grid = (splits, heads, batch), block = 128 threads.
+// K12: decode attention.  grid = (heads, splits, batch), block = 128 threads.
 // head_dim = 128: a half-warp (16 lanes x 8 elements) covers one K/V row.
 // partial layout: [batch, heads, splits, head_dim + 2] fp32 = {acc[head_dim], max, sum}.
 // ---------------------------------------------------------------------------------------------
@@ -51,8 +51,10 @@ paged_attn_decode_kernel(const __nv_bfloat16* __restrict__ q, long long q_stride
                          int heads, int block_size, int tokens_per_split, float scale_log2) {
   constexpr int kLanesPerRow = kHeadDim / 8;          // 16 for D=128, 8 for D=64
   constexpr int kRowsPerWarp = 32 / kLanesPerRow;
-  const int split = blockIdx.x, head = blockIdx.y, b = blockIdx.z;
-  const int nsplit = gridDim.x;
+  // heads vary fastest in launch order: the CTAs of all heads of one (sequence, split) are co-resident and walk
+  // the same token rows together, so each [heads x head_dim] cache row is fetched from DRAM as one burst
+  const int head = blockIdx.x, split = blockIdx.y, b = blockIdx.z;
+  const int nsplit = gridDim.y;
   const int ctx = context_lens[b];
   const int t0 = split * tokens_per_split;
   const int t1 = min(ctx, t0 + tokens_per_split);
@@ -201,7 +203,7 @@ LLMCTL_API int llmctl_paged_attn_decode(const void* q, long long q_stride, const
   per = ((per + block_size - 1) / block_size) * block_size;  // whole blocks per split
   if (per < block_size) per = block_size;
   const float scale_log2 = scale * 1.4426950408889634f;
-  dim3 grid(num_splits, heads, batch);
+  dim3 grid(heads, num_splits, batch);
   if (head_dim == 128) {
     paged_attn_decode_kernel<128><<<grid, 128, 0, s>>>(
         (const __nv_bfloat16*)q, q_stride, (const __nv_bfloat16*)k_cache, (const __nv_bfloat16*)v_cache,

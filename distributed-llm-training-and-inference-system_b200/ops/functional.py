@@ -35,6 +35,7 @@ class KernelConfig:
     elementwise: str = "native"  # native | aten   (norm / rope / swiglu / cross-entropy)
     optimizer: str = "native"   # native | torch
     gemm_tile_n: int = 0        # 0 = heuristic; 128 | 256 (auto-tuner knob)
+    skinny_gemm: bool = True    # <= 32 rows without grad: weight-streaming split-K kernel (decode)
 
 
 _cfg = KernelConfig()
@@ -372,6 +373,34 @@ class _LinearFn(torch.autograd.Function):
         return dx, dw
 
 
+_skinny_ws: dict = {}
+SKINNY_MAX_ROWS = 32
+
+
+def _skinny_workspace(device: torch.device):
+    """Per-device split-K scratch of the skinny GEMM (fp32 partials + zeroed ticket counters).  Calls are serialised
+    by the stream they run on; the decode engine uses one stream."""
+    key = (device.index if device.index is not None else torch.cuda.current_device())
+    ws = _skinny_ws.get(key)
+    if ws is None:
+        ws = _skinny_ws[key] = (torch.empty(8 << 20, dtype=torch.float32, device=device),
+                                torch.zeros(4096, dtype=torch.int32, device=device))
+    return ws
+
+
+def gemm_skinny(x: torch.Tensor, w: torch.Tensor, out: Optional[torch.Tensor] = None, splits: int = 0) -> torch.Tensor:
+    """``x @ w.T`` for at most 32 rows of x (decode): weight-streaming swap-AB split-K tcgen05 kernel."""
+    M, K = x.shape
+    N = w.shape[0]
+    assert M <= SKINNY_MAX_ROWS and w.shape[1] == K and x.stride(1) == 1 and w.stride(1) == 1
+    if out is None:
+        out = torch.empty(M, N, dtype=torch.bfloat16, device=x.device)
+    ws, cnt = _skinny_workspace(x.device)
+    native.call("llmctl_gemm_skinny_bf16", x.data_ptr(), w.data_ptr(), out.data_ptr(), M, N, K, x.stride(0), w.stride(0),
+                out.stride(0), ws.data_ptr(), ws.numel(), cnt.data_ptr(), cnt.numel(), splits, native.stream_ptr())
+    return out
+
+
 def linear(x: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
     """``x @ w.T`` (no bias).  x: [..., K], w: [N, K]."""
     if _use_native(x, "gemm") and w.dtype == torch.bfloat16:
@@ -379,6 +408,9 @@ def linear(x: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
         x2 = x.reshape(-1, shape[-1])
         if not _gemm_ok(x2):
             x2 = x2.contiguous()
+        if (x2.shape[0] <= SKINNY_MAX_ROWS and _cfg.skinny_gemm and _gemm_ok(x2, w) and native.has_symbol("llmctl_gemm_skinny_bf16")
+                and not (torch.is_grad_enabled() and (x.requires_grad or w.requires_grad))):
+            return gemm_skinny(x2, w).view(*shape[:-1], w.shape[0])
         if _gemm_ok(x2, w) and w.shape[0] % 8 == 0:
             return _LinearFn.apply(x2, w).view(*shape[:-1], w.shape[0])
     return F.linear(x, w)

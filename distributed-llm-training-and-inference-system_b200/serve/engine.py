@@ -158,6 +158,7 @@ class _DecodeAllReduce:
     two calls ahead of the slowest peer once it has passed the next call's entry barrier."""
 
     def __init__(self, st, max_rows: int, hidden: int, device: torch.device):
+        from ..comms import fused as _fused  # noqa: F401  (registers the C signatures of the peer-memory kernels)
         from ..comms.symm import SymmBuffer
         self.rank, self.world, self.hidden, self.max_rows = st.tp_rank, st.tp, hidden, max_rows
         self.bufs = [SymmBuffer(max_rows * hidden, torch.bfloat16, st.tp_group, device) for _ in range(2)]

@@ -80,7 +80,7 @@ int llmctl_cross_entropy_finalize(void* logits, long long ld, const long long* t
 /* ---- K0 tcgen05/TMA GEMM.  Reference: cuBLAS via torch.matmul / nn.Linear. ----
  * D[M,N] = op(A) op(B) (+ D if beta).  a_mn=0: A is [M,K] row-major; a_mn=1: A stored [K,M].
  * b_mn=0: B is [N,K] row-major (Linear weight); b_mn=1: B stored [K,N].
- * out_fp32: D fp32 else bf16.  tile_n: 0 auto | 128 | 256.  max_ctas: 0 = all SMs. */
+ * out_fp32: D fp32 else bf16.  tile_n: 0 auto | 128 | 256 | 2 = 256x256 tile on a CTA pair (cta_group::2).  max_ctas: 0 = all SMs. */
 int llmctl_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, long long lda,
                      long long ldb, long long ldc, int a_mn, int b_mn, int out_fp32, int beta,
                      int tile_n, int max_ctas, void* stream);
@@ -102,6 +102,80 @@ int llmctl_paged_attn_decode(const void* q, long long q_stride, const void* k_ca
 int llmctl_sample(const void* logits, int logits_is_fp32, long long ld, int rows, int V,
                   const float* temperature, const int* top_k, const float* top_p, const float* uniform,
                   long long* out_token, float* out_logprob, void* stream);
+
+/* ---- K0s skinny (decode) GEMM: C[Mb,N] = X[Mb,K] W[N,K]^T, 1 <= Mb <= 32.  Swap-AB (UMMA M = 128 weight rows,
+ * N = 16/32 token rows), split-K over CTAs with a deterministic in-kernel fix-up.  workspace: fp32 scratch;
+ * counters: >= ceil(N/128) zeroed uint32 tickets (left zero on return); one call at a time per pair.
+ * Reference: cuBLAS inside the HF model (server.py:199-204). */
+int llmctl_gemm_skinny_bf16(const void* X, const void* W, void* C, int Mb, int N, int K, long long ldx,
+                            long long ldw, long long ldc, float* workspace, long long workspace_elems,
+                            unsigned int* counters, int n_counters, int splits, void* stream);
+
+/* ---- K6 causal flash attention, head_dim 128, bf16.  q/k/v/o: [B,S,H,128] views with token strides in
+ * elements; lse: fp32 [B,H,S] (natural log).  S % 128 == 0.  Reference: SDPA/eager inside the HF model
+ * (engine.py:284); baseline cuDNN SDPA.
+ * Forward: 256 queries per CTA as two tiles sharing K/V, S/P/O in TMEM, P never leaves TMEM.
+ * Backward: two deterministic kernels (dK/dV on transposed scores, then dQ); scratch >= 2*B*H*S floats
+ * (the single-kernel atomic variant selected by LLMCTL_FLASH_BWD_V1 needs B*S*H*129). */
+int llmctl_flash_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int B, int S, int H,
+                          int D, long long q_tok_stride, long long k_tok_stride, long long v_tok_stride,
+                          long long o_tok_stride, float scale, int causal, void* stream);
+int llmctl_flash_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* d_o,
+                          const float* lse, void* dq, void* dk, void* dv, float* scratch, int B, int S, int H,
+                          int D, long long q_tok_stride, long long k_tok_stride, long long v_tok_stride,
+                          long long o_tok_stride, long long dqkv_tok_stride, float scale, int causal, void* stream);
+
+/* ---- Peer-memory (NVLink 5 / NVSwitch) kernels.  No counterpart in the reference (llmctl/comms is empty).
+ * llmctl_peer_table: base pointers of one symmetric allocation on every rank of the group (unused = NULL);
+ * `pads` is the table of per-rank signal pads (uint32 flags); `epoch` must increase by one per call on every
+ * rank for a given slot range.  A wait that exceeds the watchdog deadline gives up and is reported by
+ * llmctl_comm_watchdog_poll instead of hanging the GPU. */
+typedef struct { void* ptr[8]; } llmctl_peer_table;
+
+/* stand-alone collectives on a symmetric bf16 workspace (pad slots [slot, slot + world)) */
+int llmctl_allgather_pull(llmctl_peer_table buf, long long chunk_bytes, llmctl_peer_table pads, int slot, int rank,
+                          int world, unsigned int epoch, int max_ctas, void* stream);
+int llmctl_reduce_scatter_pull(llmctl_peer_table in, long long n_per_rank, void* out, llmctl_peer_table pads,
+                               int slot, int rank, int world, unsigned int epoch, int max_ctas, void* stream);
+int llmctl_allreduce_oneshot(llmctl_peer_table in, long long n, void* out, llmctl_peer_table pads, int slot,
+                             int rank, int world, unsigned int epoch, int max_ctas, void* stream);
+int llmctl_allreduce_multimem(void* mc, long long n, llmctl_peer_table pads, int slot, int rank, int world,
+                              unsigned int epoch, int max_ctas, void* stream);   /* NVLS multimem.ld_reduce/st */
+
+/* K1: all-gather (TMA bulk pulls by n_copy copy CTAs, 0 = default) fused with the column-parallel GEMM.
+ * xg: symmetric [M,K]; local_flags: 32 zeroed uint32 in local memory. */
+int llmctl_ag_gemm(llmctl_peer_table xg, const void* W, void* C, int M, int N, int K, long long ldw, long long ldc,
+                   llmctl_peer_table pads, unsigned int* local_flags, int rank, int world, unsigned int epoch,
+                   int n_copy, void* stream);
+/* K2: row-parallel GEMM whose epilogue pushes bf16 tiles into the owner's staging slot; finished by
+ * llmctl_rs_reduce_rmsnorm (sum of the world slots + residual (+ RMSNorm)) on the sequence shard. */
+int llmctl_gemm_rs(const void* X, const void* W, llmctl_peer_table stage, int M, int N, int K, long long ldx,
+                   long long ldw, llmctl_peer_table pads, unsigned int* local_flags, int rank, int world,
+                   unsigned int epoch, void* stream);
+int llmctl_rs_reduce_rmsnorm(const void* stage_local, llmctl_peer_table pads, int rank, int world,
+                             const void* residual, const void* w, void* h_out, void* y, float* rstd, int rows,
+                             int cols, float eps, unsigned int epoch, void* stream);
+/* K7: ZeRO gradient reduce-scatter (pull) + squared-norm partial, then AdamW on the shard + parameter
+ * all-gather (push, or NVLS multimem.st when mc_params != NULL). */
+int llmctl_rs_sumsq(llmctl_peer_table grads, long long bucket_off, llmctl_peer_table pads, int rank, int world,
+                    long long shard_lo, long long shard_n, float* reduced, float* scratch, int scratch_elems,
+                    float* sumsq_out, int accumulate, unsigned int epoch, void* stream);
+int llmctl_adam_allgather(llmctl_peer_table params, long long bucket_off, void* mc_params, llmctl_peer_table pads,
+                          llmctl_peer_table scalars, int rank, int world, long long shard_lo, long long shard_n,
+                          float* master, float* m, float* v, const float* reduced, float lr, float beta1,
+                          float beta2, float eps, float weight_decay, float bias_corr1, float bias_corr2,
+                          float grad_scale, float max_norm, float* norm_out, unsigned int epoch,
+                          int begin_barrier, int end_barrier, void* stream);
+/* K11: decode all-reduce of [rows, cols] partial sums + residual add + RMSNorm in one launch. */
+int llmctl_ar_residual_rmsnorm(llmctl_peer_table x, long long x_off, const void* mc_x, llmctl_peer_table pads,
+                               int slot_base, int rank, int world, const void* residual, void* h_out,
+                               const void* w, void* y_out, int rows, int cols, float eps, unsigned int epoch,
+                               void* stream);
+/* watchdog: out[0] timed-out waits since the last clearing poll, out[1..6] = expected epoch, value seen,
+ * blockIdx.x, flag address, ns waited, module index of the first one (out must hold 8 values). */
+int llmctl_comm_watchdog_poll(unsigned long long* out, char* module_name, int name_cap, int clear);
+int llmctl_comm_watchdog_set_timeout_ms(unsigned long long ms);
+int llmctl_comm_watchdog_modules(void);
 
 #ifdef __cplusplus
 }

@@ -171,6 +171,24 @@ def test_gemm_layouts(cuda_device, M, N, K, a_mn, b_mn):
         _close(out, ref, 0.05 * math.sqrt(K / 64), 2e-2, f"gemm tile_n={tile_n}")
 
 
+@pytest.mark.parametrize("M,N,K,splits", [(8, 4096, 4096, 0), (1, 4096, 4096, 4), (16, 12288, 4096, 0), (17, 4096, 11008, 0),
+                                            (32, 1000, 512, 3), (5, 32000, 4096, 1), (8, 22016, 4096, 0)])
+def test_gemm_skinny(cuda_device, M, N, K, splits):
+    """Decode GEMM (swap-AB, split-K with in-kernel deterministic fix-up) vs fp32 matmul; twice in a row so the
+    self-resetting ticket counters are exercised, and bit-identical between the two calls."""
+    from llmctl_b200.ops import functional as ops
+    torch.manual_seed(8)
+    x = torch.randn(M, K, device=cuda_device).to(torch.bfloat16)
+    w = torch.randn(N, K, device=cuda_device).to(torch.bfloat16)
+    ref = x.float() @ w.float().t()
+    out1 = ops.gemm_skinny(x, w, splits=splits)
+    out2 = ops.gemm_skinny(x, w, splits=splits)
+    _close(out1, ref, 0.05 * math.sqrt(K / 64), 2e-2, "skinny gemm")
+    assert torch.equal(out1, out2)
+    with torch.no_grad():
+        assert torch.equal(ops.linear(x, w), out1) or splits != 0
+
+
 def test_gemm_fp32_accumulate(cuda_device):
     from llmctl_b200.ops import functional as ops
     torch.manual_seed(7)
