@@ -501,6 +501,34 @@ template <int N>
 __device__ __forceinline__ void setmaxnreg_dec() {
   asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N));
 }
+// (a0,a1) * (b0,b1) + (c0,c1)
+__device__ __forceinline__ void fma2vv(float& d0, float& d1, float a0, float a1, float b0, float b1, float c0, float c1) {
+  asm("{\n\t.reg .b64 ra, rb, rc, rd;\n\t"
+      "mov.b64 ra, {%2, %3};\n\tmov.b64 rb, {%4, %5};\n\tmov.b64 rc, {%6, %7};\n\t"
+      "fma.rn.f32x2 rd, ra, rb, rc;\n\t"
+      "mov.b64 {%0, %1}, rd;\n\t}"
+      : "=f"(d0), "=f"(d1)
+      : "f"(a0), "f"(a1), "f"(b0), "f"(b1), "f"(c0), "f"(c1));
+}
+// 2^x for two values WITHOUT the SFU: the exponential unit (16 results / clk / SM) is as scarce as the tensor
+// core in attention (one exp per score), so part of the row is evaluated on the FMA pipes instead.
+// Round-to-nearest split x = n + f, |f| <= 0.5 via the 1.5*2^23 trick (n sits in the low mantissa bits of t),
+// cubic minimax 2^f (max relative error 7.5e-5, below bf16 resolution), exponent patched in with one integer
+// multiply-add.  Inputs are clamped to >= -126 (masked scores give ~1e-38, i.e. zero weight).
+__device__ __forceinline__ void ex2_poly2(float& p0, float& p1, float x0, float x1) {
+  constexpr float kMagic = 12582912.f;   // 1.5 * 2^23
+  x0 = fmaxf(x0, -126.f);
+  x1 = fmaxf(x1, -126.f);
+  float t0, t1, r0, r1, f0, f1, q0, q1;
+  add2v(t0, t1, x0, x1, kMagic, kMagic);
+  add2v(r0, r1, t0, t1, -kMagic, -kMagic);
+  fma2v(f0, f1, r0, r1, -1.f, x0, x1);
+  fma2(q0, q1, f0, f1, 0.05517167f, 0.24261112f);
+  fma2vv(q0, q1, q0, q1, f0, f1, 0.69326099f, 0.69326099f);
+  fma2vv(q0, q1, q0, q1, f0, f1, 0.99992807f, 0.99992807f);
+  p0 = __int_as_float(__float_as_int(q0) + (__float_as_int(t0) << 23));
+  p1 = __int_as_float(__float_as_int(q1) + (__float_as_int(t1) << 23));
+}
 __device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }

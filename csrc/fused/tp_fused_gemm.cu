@@ -37,8 +37,11 @@ constexpr int kFBBytes = kFBN * kFBK * 2;
 constexpr int kFStageBytes = kFABytes + kFBBytes;
 constexpr int kFSmem = kFStages * kFStageBytes + 1024;
 constexpr int kFThreads = 192;
-constexpr int kCopyPiece = 32768;            // bytes per TMA bulk copy
-constexpr int kCopyStages = 4;               // smem ring of the copy CTAs (4 x 32 KB)
+constexpr int kCopyPiece = 16384;            // bytes per TMA bulk copy
+constexpr int kCopySlots = 12;               // smem ring of the copy CTAs (12 x 16 KB)
+constexpr int kCopyAhead = 8;                // loads in flight; the 4 spare slots decouple a load from the store
+                                             // that last used its slot (no wait on the store just issued)
+constexpr int kCopyStages = 4;               // store groups allowed in flight when a chunk is published
 constexpr int kEpiRowBytes = 128 + 16;       // K2 epilogue staging: 64 bf16 per row + pad (conflict-free 16 B access)
 constexpr int kEpiWarpBytes = 32 * kEpiRowBytes;
 constexpr int kFSmemRS = kFSmem + 4 * kEpiWarpBytes;
@@ -77,7 +80,7 @@ tp_fused_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
   __shared__ uint64_t bar_empty[kFStages];
   __shared__ uint64_t bar_tfull[2];
   __shared__ uint64_t bar_tempty[2];
-  __shared__ uint64_t bar_copy[kCopyStages];
+  __shared__ uint64_t bar_copy[kCopySlots];
   __shared__ uint32_t tmem_base_smem;
 
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -89,7 +92,7 @@ tp_fused_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
   // ================================ K1 copy CTAs ================================
   if (kMode == 1 && static_cast<int>(blockIdx.x) < a.n_copy) {
     if (threadIdx.x == 0) {
-      for (int i = 0; i < kCopyStages; ++i) mbar_init(&bar_copy[i], 1);
+      for (int i = 0; i < kCopySlots; ++i) mbar_init(&bar_copy[i], 1);
       fence_mbar_init();
       // announce that this rank's own rows are in place (written by the previous kernel on this stream)
       if (blockIdx.x == 0)
@@ -129,7 +132,7 @@ tp_fused_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
         publish_upto(a.world - 1);                     // nothing to copy: still take part in the chunk counters
       } else {
         while (stored < total) {
-          while (issued < total && issued - stored < kCopyStages) {
+          while (issued < total && issued - stored < kCopyAhead) {
             int src; long long off; uint32_t bytes;
             item(issued, src, off, bytes);
             const int ci = 1 + issued / per_cta;
@@ -137,8 +140,10 @@ tp_fused_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
               signal_wait_ge(reinterpret_cast<const uint32_t*>(pads.ptr[a.rank]) + src, a.epoch);
               waited_chunk = ci;
             }
-            const int slot = issued % kCopyStages;
-            tma_store_wait_read<0>();                 // every earlier smem->global store has finished READING its slot
+            const int slot = issued % kCopySlots;
+            // the store that last used this slot is at least (kCopySlots - kCopyAhead) groups old: only it (and
+            // older ones) must have finished READING shared memory
+            tma_store_wait_read<kCopySlots - kCopyAhead>();
             mbar_expect_tx(&bar_copy[slot], bytes);
             bulk_load_1d(smem + slot * kCopyPiece,
                          reinterpret_cast<const uint8_t*>(xg.ptr[src]) + static_cast<long long>(src) * chunk_bytes + off,
@@ -147,7 +152,7 @@ tp_fused_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
           }
           int src; long long off; uint32_t bytes;
           item(stored, src, off, bytes);
-          const int slot = stored % kCopyStages;
+          const int slot = stored % kCopySlots;
           mbar_wait(&bar_copy[slot], (phase_bits >> slot) & 1u);
           phase_bits ^= (1u << slot);
           bulk_store_1d(reinterpret_cast<uint8_t*>(xg.ptr[a.rank]) + static_cast<long long>(src) * chunk_bytes + off,

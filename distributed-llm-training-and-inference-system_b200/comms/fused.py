@@ -13,6 +13,7 @@ Reference: ``llmctl.comms`` is an empty package (reference llmctl/comms/__init__
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import Optional
 
 import torch
@@ -46,7 +47,7 @@ class TPFusedContext:
         self.ep_rs = 0
         self.i_ag = 0
         self.i_rs = 0
-        self.n_copy = 12
+        self.n_copy = int(os.environ.get("LLMCTL_K1_COPY_CTAS", "0"))   # 0 = the kernel's default for this world size
         torch.cuda.synchronize(device)
         self.xg[0].barrier()
 

@@ -71,6 +71,12 @@ def case_tp_kernels(out, M=4096, K=4096, N=1536, Kl=1376):
         dist.all_gather_into_tensor(g, x_local)
         return g @ w.t()
     res["ag_gemm_ms"] = time_max(lambda: ctx.ag_gemm(x_local, w))
+    sweep = {}
+    for nc in (8, 16, 24, 32, 48):
+        ctx.n_copy = nc
+        sweep[str(nc)] = time_max(lambda: ctx.ag_gemm(x_local, w))
+    ctx.n_copy = 0
+    res["ag_gemm_ms_by_copy_ctas"] = sweep
     res["nccl_ag_then_cublas_ms"] = time_max(base_ag)
     res["gemm_only_cublas_ms"] = time_max(lambda: gathered @ w.t())
     # ---- K2 ----
