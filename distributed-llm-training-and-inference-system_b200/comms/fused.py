@@ -50,6 +50,47 @@ class TPFusedContext:
         self.n_copy = int(os.environ.get("LLMCTL_K1_COPY_CTAS", "0"))   # 0 = the kernel's default for this world size
         torch.cuda.synchronize(device)
         self.xg[0].barrier()
+        # K1 is only the default where it wins: at tp = 8 on this pool the gather of 7 remote shards is bound by
+        # NVLink read round trips and the fused kernel measured 165 us against 120 us for NCCL all-gather + GEMM,
+        # at tp = 2 it wins (82 vs 99 us).  LLMCTL_K1 = fused | nccl | auto (default: time both once, all ranks agree).
+        mode = os.environ.get("LLMCTL_K1", "auto").lower()
+        self.k1_timing = None
+        if mode == "fused" or world == 1:
+            self.use_k1 = True
+        elif mode == "nccl":
+            self.use_k1 = False
+        else:
+            self.use_k1 = self._autotune_k1()
+
+    def _ag_gemm_nccl(self, x_local: torch.Tensor, w: torch.Tensor):
+        Ms, K = x_local.shape
+        full = torch.empty(Ms * self.world, K, dtype=x_local.dtype, device=x_local.device)
+        dist.all_gather_into_tensor(full, x_local.contiguous(), group=self.group)
+        return ops.gemm_raw(full, w), full
+
+    def _autotune_k1(self) -> bool:
+        rows = max(min(self.max_tokens // self.world, 1024) // 8 * 8, 8)
+        K = self.hidden
+        N = max(min(self.hidden, 4096) // 8 * 8, 8)
+        x = torch.randn(rows, K, device=self.device).bfloat16()
+        w = torch.randn(N, K, device=self.device).bfloat16()
+        times = []
+        for fn in (lambda: self._ag_gemm_fused(x, w), lambda: self._ag_gemm_nccl(x, w)):
+            for _ in range(3):
+                fn()
+            torch.cuda.synchronize(self.device)
+            dist.barrier(group=self.group)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(8):
+                fn()
+            e1.record()
+            torch.cuda.synchronize(self.device)
+            times.append(e0.elapsed_time(e1) / 8)
+        t = torch.tensor(times, device=self.device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+        self.k1_timing = {"fused_ms": float(t[0]), "nccl_ms": float(t[1])}
+        return bool(t[0] <= 1.02 * t[1])
 
     def usable(self, x: torch.Tensor) -> bool:
         return (ops.kernel_config().gemm == "native" and x.dim() == 2 and x.shape[0] * self.world <= self.max_tokens
@@ -64,6 +105,13 @@ class TPFusedContext:
         return buf, full, full[self.rank * rows_local:(self.rank + 1) * rows_local]
 
     def ag_gemm(self, x_local: torch.Tensor, w: torch.Tensor):
+        """x_local [Ms, K] -> (y [M, N], Xg [M, K]): the fused kernel, or NCCL all-gather + tcgen05 GEMM where the
+        start-up measurement found that faster (see ``use_k1``)."""
+        if not self.use_k1:
+            return self._ag_gemm_nccl(x_local, w)
+        return self._ag_gemm_fused(x_local, w)
+
+    def _ag_gemm_fused(self, x_local: torch.Tensor, w: torch.Tensor):
         """x_local [Ms, K] (copied into the symmetric buffer unless it already lives there) -> (y [M, N], Xg [M, K])."""
         Ms, K = x_local.shape
         N = w.shape[0]
@@ -109,7 +157,7 @@ class _AGLinearFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x_local, w):
         y, xg_full = _ctx.ag_gemm(x_local, w)
-        ctx.save_for_backward(xg_full.clone() if _ctx.world > 1 else xg_full, w)   # Xg is recycled two calls later
+        ctx.save_for_backward(xg_full.clone() if (_ctx.world > 1 and _ctx.use_k1) else xg_full, w)   # the symmetric Xg is recycled two calls later
         return y
 
     @staticmethod

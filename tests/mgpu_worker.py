@@ -56,7 +56,7 @@ def case_tp_kernels(out, M=4096, K=4096, N=1536, Kl=1376):
     # ---- K1 ----
     res = {}
     for it in range(3):                                  # several calls: exercises the alternating buffers / epochs
-        y, xg = ctx.ag_gemm(x_local, w)
+        y, xg = ctx._ag_gemm_fused(x_local, w)
         gathered = torch.empty(M, K, device="cuda", dtype=torch.bfloat16)
         dist.all_gather_into_tensor(gathered, x_local)
         ref = gathered.float() @ w.float().t()
@@ -70,11 +70,12 @@ def case_tp_kernels(out, M=4096, K=4096, N=1536, Kl=1376):
         g = torch.empty(M, K, device="cuda", dtype=torch.bfloat16)
         dist.all_gather_into_tensor(g, x_local)
         return g @ w.t()
-    res["ag_gemm_ms"] = time_max(lambda: ctx.ag_gemm(x_local, w))
+    res["ag_gemm_ms"] = time_max(lambda: ctx._ag_gemm_fused(x_local, w))
+    res["k1_autotune"] = {"use_k1": ctx.use_k1, "timing": ctx.k1_timing}
     sweep = {}
     for nc in (8, 16, 24, 32, 48):
         ctx.n_copy = nc
-        sweep[str(nc)] = time_max(lambda: ctx.ag_gemm(x_local, w))
+        sweep[str(nc)] = time_max(lambda: ctx._ag_gemm_fused(x_local, w))
     ctx.n_copy = 0
     res["ag_gemm_ms_by_copy_ctas"] = sweep
     res["nccl_ag_then_cublas_ms"] = time_max(base_ag)
