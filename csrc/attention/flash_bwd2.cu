@@ -75,7 +75,7 @@ flash_bwd2_kernel(const __grid_constant__ CUtensorMap tmRes0, const __grid_const
                   const float2* __restrict__ stats, int S, int H, float scale_log2, float scale, int causal) {
   using namespace bwd2;
   extern __shared__ uint8_t smem_raw[];
-  __shared__ uint64_t bar_res, bar_full[kStages], bar_empty[kStages], bar_s[2], bar_p[2], bar_done;
+  __shared__ uint64_t bar_res, bar_full[kStages], bar_empty[kStages], bar_s[2], bar_p[2], bar_done, bar_tres;
   __shared__ uint32_t tmem_base_smem;
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem = smem_raw + (smem_base - smem_u32(smem_raw));
@@ -103,6 +103,7 @@ flash_bwd2_kernel(const __grid_constant__ CUtensorMap tmRes0, const __grid_const
       mbar_init(&bar_p[i], 4);
     }
     mbar_init(&bar_done, 1);
+    mbar_init(&bar_tres, 8);
     fence_mbar_init();
   }
   if (warp == 0 && lane == 0) {
@@ -120,6 +121,10 @@ flash_bwd2_kernel(const __grid_constant__ CUtensorMap tmRes0, const __grid_const
   const uint32_t tmem_base = tmem_base_smem;
   // TMEM: S buffers [0,64) [64,128);  dP buffers [128,192) [192,256);  acc0 [256,384);  acc1 [384,512)
   const uint32_t tS = tmem_base, tdP = tmem_base + 128, tAcc0 = tmem_base + 256, tAcc1 = tmem_base + 384;
+  // dQ kernel only (acc1 is unused there): the resident Q and dO tiles are copied once into TMEM as bf16x2
+  // A operands ([384,448) and [448,512)), so S = Q K^T and dP = dO V^T read only their 2 KB B operand from
+  // shared memory per MMA (64 B/clk) instead of 6 KB (192 B/clk, the operand-bandwidth limit of N = 64 tiles)
+  const uint32_t tRes0 = tmem_base + 384, tRes1 = tmem_base + 448;
 
   if (warp == 0) {
     if (lane == 0) {
@@ -163,15 +168,28 @@ flash_bwd2_kernel(const __grid_constant__ CUtensorMap tmRes0, const __grid_const
         mbar_wait(&bar_full[st], (n / kStages) & 1u);
         tc_fence_after();
         const uint32_t a0 = aRing + st * kStageBytes, a1 = a0 + kSubTile;
+        if (kDQ) {
 #pragma unroll
-        for (int ks = 0; ks < 8; ++ks)
-          umma_ss<1>(tS + buf * 64, kdesc_res(aRes0, ks), kdesc_sub(a0, ks), id_s, ks != 0 ? 1u : 0u);
+          for (int ks = 0; ks < 8; ++ks)
+            umma_ts<1>(tS + buf * 64, tRes0 + ks * 8, kdesc_sub(a0, ks), id_s, ks != 0 ? 1u : 0u);
 #pragma unroll
-        for (int ks = 0; ks < 8; ++ks)
-          umma_ss<1>(tdP + buf * 64, kdesc_res(aRes1, ks), kdesc_sub(a1, ks), id_s, ks != 0 ? 1u : 0u);
+          for (int ks = 0; ks < 8; ++ks)
+            umma_ts<1>(tdP + buf * 64, tRes1 + ks * 8, kdesc_sub(a1, ks), id_s, ks != 0 ? 1u : 0u);
+        } else {
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks)
+            umma_ss<1>(tS + buf * 64, kdesc_res(aRes0, ks), kdesc_sub(a0, ks), id_s, ks != 0 ? 1u : 0u);
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks)
+            umma_ss<1>(tdP + buf * 64, kdesc_res(aRes1, ks), kdesc_sub(a1, ks), id_s, ks != 0 ? 1u : 0u);
+        }
         umma_commit<1>(&bar_s[buf]);
       };
       mbar_wait(&bar_res, 0);
+      if (kDQ) {
+        mbar_wait(&bar_tres, 0);         // Q and dO have been copied into TMEM by the softmax warps
+        tc_fence_after();
+      }
       issue_s(0);
       if (nsub > 1) issue_s(1);
       for (int n = 0; n < nsub; ++n) {
@@ -207,6 +225,26 @@ flash_bwd2_kernel(const __grid_constant__ CUtensorMap tmRes0, const __grid_const
       const float2 sv = stats[(static_cast<long long>(b) * H + head) * S + r0 + row];
       nl2 = sv.x;
       ndl = sv.y;
+      // warpgroup 0 moves Q, warpgroup 1 moves dO: this thread's row, 16 swizzled 16-byte chunks -> 64 TMEM columns
+      mbar_wait(&bar_res, 0);
+      const uint8_t* src = (wg == 0 ? sRes0 : sRes1) + row * 128;
+      const uint32_t dst = (wg == 0 ? tRes0 : tRes1) + lane_off;
+#pragma unroll
+      for (int pnl = 0; pnl < 2; ++pnl) {
+#pragma unroll
+        for (int c2 = 0; c2 < 4; ++c2) {
+          uint32_t w[8];
+          const uint4 lo = *reinterpret_cast<const uint4*>(src + pnl * kResPanel + (((2 * c2) ^ (row & 7)) << 4));
+          const uint4 hi = *reinterpret_cast<const uint4*>(src + pnl * kResPanel + (((2 * c2 + 1) ^ (row & 7)) << 4));
+          w[0] = lo.x; w[1] = lo.y; w[2] = lo.z; w[3] = lo.w;
+          w[4] = hi.x; w[5] = hi.y; w[6] = hi.z; w[7] = hi.w;
+          tmem_st_x8(dst + pnl * 32 + c2 * 8, w);
+        }
+      }
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&bar_tres);
     }
     for (int n = wg; n < nsub; n += 2) {
       const int st = n % kStages;

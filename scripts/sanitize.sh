@@ -2,6 +2,7 @@
 # compute-sanitizer targets for the single-GPU kernels: one tool per invocation.
 #   scripts/sanitize.sh memcheck|racecheck|synccheck|initcheck [pytest -k expression]
 # Runs the kernel numerics tests under the tool; a non-zero exit (or an "ERROR SUMMARY" with errors) fails.
+# NOTE: on the graft B200 pool compute-sanitizer is closed (the wrapper refuses to run it); the script is for other boxes.
 # Cross-GPU kernels are not run under the sanitizer (it serialises kernels, and mutually-waiting kernels on
 # different GPUs then time out); their protocol is exercised by tests/mgpu_worker.py `watchdog` instead.
 set -u
