@@ -243,7 +243,9 @@ class ServeConfig(_Base):
     @classmethod
     def _sched(cls, v):
         if v not in ("dynamic", "simple", "vllm-like"):
-            raise ValueError("scheduler must be dynamic | simple | vllm-like")
+            from ..plugins.registry import get_registry
+            if get_registry().get("schedulers", v) is None:
+                raise ValueError("scheduler must be dynamic | simple | vllm-like or a registered scheduler plugin")
         return v
 
 

@@ -86,6 +86,15 @@ class Sequence:
         return self.prompt_ids + self.generated
 
 
+@dataclass
+class _StagedRequest:
+    """What a scheduler plugin sees of a waiting request."""
+    request_id: int
+    prompt_len: int
+    max_tokens: int
+    arrival: float
+
+
 class _HostViews:
     """numpy views into one pinned staging buffer."""
 
@@ -205,6 +214,19 @@ class InferenceEngine:
             want = (max_batch_tokens + kv_block_size - 1) // kv_block_size + max_batch_size
             num_kv_blocks = max(min(num_kv_blocks, 8 * want), want)
         self.kv = KVBlockManager(num_kv_blocks, kv_block_size)
+        # a scheduler plugin (user-guide contract: ``schedule(requests) -> ordered requests``) decides the ORDER in
+        # which waiting requests are handed to the native continuous-batching core; budgets, KV accounting and
+        # preemption stay in the C++ scheduler
+        self._plugin_sched = None
+        self._staged: List["_StagedRequest"] = []
+        self.max_batch_size = max_batch_size
+        if scheduler not in ("dynamic", "simple", "vllm-like"):
+            from ..plugins.registry import get_registry
+            factory = get_registry().get("schedulers", scheduler)
+            if factory is None:
+                raise ValueError(f"unknown scheduler {scheduler!r}: not a built-in policy and no plugin registers it")
+            self._plugin_sched = factory() if callable(factory) else factory
+            scheduler = "dynamic"
         self.sched = BatchScheduler(max_batch_size, max_batch_tokens, scheduler, self.kv)
         shape = (num_kv_blocks, kv_block_size, self.heads_local, self.head_dim)
         self.k_caches = [torch.zeros(shape, dtype=self.dtype, device=self.device) for _ in m.blocks]
@@ -249,6 +271,10 @@ class InferenceEngine:
             rid = self._next_id
             self._next_id += 1
             seq = Sequence(rid, list(prompt_ids), max_tokens, temperature, top_p, top_k, on_token=on_token)
+            if self._plugin_sched is not None and max_tokens > 0:
+                self._staged.append(_StagedRequest(rid, len(prompt_ids), max_tokens, time.time()))
+                self.seqs[rid] = seq
+                return seq
             if max_tokens <= 0 or not self.sched.add_request(rid, len(prompt_ids), max_tokens):
                 seq.finished, seq.finish_reason = True, "error"
                 seq.done_event.set()
@@ -257,7 +283,21 @@ class InferenceEngine:
         return seq
 
     def has_work(self) -> bool:
-        return self.sched.num_waiting + self.sched.num_running > 0
+        return self.sched.num_waiting + self.sched.num_running + len(self._staged) > 0
+
+    def _admit_staged(self) -> None:
+        """Hand staged requests to the native scheduler in the order the plugin chooses, as slots free up."""
+        room = self.max_batch_size - (self.sched.num_waiting + self.sched.num_running)
+        if room <= 0 or not self._staged:
+            return
+        ordered = list(self._plugin_sched.schedule(list(self._staged)))
+        for r in ordered[:room]:
+            self._staged.remove(r)
+            if not self.sched.add_request(r.request_id, r.prompt_len, r.max_tokens):
+                seq = self.seqs.pop(r.request_id, None)
+                if seq is not None:
+                    seq.finished, seq.finish_reason = True, "error"
+                    seq.done_event.set()
 
     # ---- model pieces ----------------------------------------------------------------------------------
     def _slots(self, rid: int, start: int, count: int) -> torch.Tensor:
@@ -415,6 +455,9 @@ class InferenceEngine:
     # ---- one engine step ---------------------------------------------------------------------------------
     def step(self) -> List[Sequence]:
         """Runs one scheduler step; returns sequences that finished in it."""
+        if self._plugin_sched is not None:
+            with self._lock:
+                self._admit_staged()
         plan = self.sched.step()
         if not plan:
             return []

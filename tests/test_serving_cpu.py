@@ -116,6 +116,31 @@ def test_engine_continuous_batching_under_pressure():
     assert too_big.finished and too_big.finish_reason == "error"
 
 
+def test_scheduler_plugin_orders_admission():
+    """A registered scheduler plugin (``schedule(requests) -> ordered requests``) decides which waiting request the
+    native continuous-batching core sees first; budgets and KV accounting stay native."""
+    from llmctl_b200.plugins.registry import get_registry
+
+    class ShortestFirst:
+        def schedule(self, requests):
+            return sorted(requests, key=lambda r: r.prompt_len)
+
+    get_registry().register("schedulers", "shortest-first", ShortestFirst, overwrite=True)
+    eng = _tiny_engine(max_batch_size=1, max_batch_tokens=256, scheduler="shortest-first")
+    long_ = eng.add_request(list(range(3, 33)), max_tokens=3, temperature=0.0)
+    short = eng.add_request([5, 6, 7], max_tokens=3, temperature=0.0)
+    first_done = None
+    steps = 0
+    while eng.has_work():
+        for s in eng.step():
+            first_done = first_done or s
+        steps += 1
+        assert steps < 100
+    assert first_done is short, "the plugin's order (shortest prompt first) was not followed"
+    assert long_.finished and len(long_.generated) == 3 and len(short.generated) == 3
+    assert eng.kv.free_blocks == 64
+
+
 def test_http_api_contract():
     from fastapi.testclient import TestClient
     from llmctl_b200.serve.server import InferenceServer
