@@ -48,6 +48,7 @@ def parse_args():
     ap.add_argument("--pp", type=int, default=1)
     ap.add_argument("--sp", action="store_true")
     ap.add_argument("--activation-checkpoint", default="none")
+    ap.add_argument("--grad-accum", type=int, default=None, help="micro-batches per step (default 1; 2*pp with a pipeline)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--gemm", default=None, help="override GEMM backend: native|cublas")
     ap.add_argument("--attention", default=None, help="override attention backend: native|sdpa")
@@ -119,9 +120,10 @@ def run_native(args) -> dict:
     dp = world // (args.tp * args.pp)
     zero = args.zero_stage if args.zero_stage is not None else (1 if dp > 1 else 0)
     import tempfile
+    n_micro = args.grad_accum if args.grad_accum else (2 * args.pp if args.pp > 1 else 1)
     tc = create_training_config(
         model_name_or_path=args.model, output_dir=tempfile.mkdtemp(prefix="llmctl_bench_"),
-        batch_size=args.micro_batch, seq_len=args.seq_len, gradient_accumulation_steps=1, max_steps=10 ** 9,
+        batch_size=args.micro_batch, seq_len=args.seq_len, gradient_accumulation_steps=n_micro, max_steps=10 ** 9,
         learning_rate=2e-4, weight_decay=0.1, gradient_clipping=1.0, warmup_steps=0, scheduler="constant",
         mixed_precision="bf16", tensor_parallel=args.tp, pipeline_parallel=args.pp, sequence_parallel=args.sp,
         zero_stage=zero, activation_checkpoint=args.activation_checkpoint,
@@ -139,7 +141,7 @@ def run_native(args) -> dict:
     dev = st.device
     mcfg = eng.model_config
     K, W = args.steps, args.warmup
-    tokens_per_step = args.micro_batch * args.seq_len * st.dp
+    tokens_per_step = args.micro_batch * args.seq_len * st.dp * n_micro
 
     def barrier():
         if world > 1:
@@ -151,6 +153,10 @@ def run_native(args) -> dict:
     torch.cuda.synchronize()
 
     def step_resident(i):
+        if st.pp > 1 or n_micro > 1:
+            # pipeline / accumulation steps go through the engine's own micro-batch schedule (1F1B); the loader
+            # keeps the next batches staged on the device, nothing is read back inside the timed region
+            return eng.train_step()["loss"]
         tok, tgt = staged[i % len(staged)]
         eng.optimizer.set_micro_batch(0, 1)
         loss = eng.model(tok, targets=tgt, loss_scale=1.0)
@@ -178,7 +184,7 @@ def run_native(args) -> dict:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms_per_step = float(ms.item()) / K
     value = tokens_per_step / (ms_per_step / 1e3)
-    final_loss = float(loss.detach())
+    final_loss = float(eng._reduce_scalar(loss)) if st.pp > 1 else float(loss.detach())
 
     # ---------------- end to end through the public API: H2D every step + D2H loss read -----------------
     e2e = None
@@ -201,7 +207,7 @@ def run_native(args) -> dict:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_ms = float(t.item()) / K
         e2e = {"value": tokens_per_step / (e2e_ms / 1e3), "unit": "tokens/s", "ms_per_step": e2e_ms,
-               "h2d_bytes_per_step": args.micro_batch * (args.seq_len + 1) * 8,
+               "h2d_bytes_per_step": n_micro * args.micro_batch * (args.seq_len + 1) * 8,
                "d2h_bytes_per_step": 4, "api": "llmctl_b200.runtime.engine.TrainingEngine.train_step"}
 
     par = f"dp{st.dp}" + (f"-zero{zero}" if st.dp > 1 else "") + (f"-tp{st.tp}" if st.tp > 1 else "") + \
@@ -213,7 +219,7 @@ def run_native(args) -> dict:
         "warmup": W, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "bf16", "data": "synthetic tokens, random-init weights",
         "impl": args.impl,
-        "config": {"model": mcfg.name, "params": mcfg.num_parameters(), "global_batch": args.micro_batch * st.dp,
+        "config": {"model": mcfg.name, "params": mcfg.num_parameters(), "global_batch": args.micro_batch * st.dp * n_micro,
                    "micro_batch": args.micro_batch, "seq_len": args.seq_len, "parallelism": par,
                    "optimizer": "AdamW fp32 master + moments, clip 1.0", "activation_checkpoint": args.activation_checkpoint,
                    "l2": "inputs larger than L2: every step streams >100 GB of weights/optimizer state (L2 = 126 MB)",
