@@ -218,3 +218,50 @@ def test_shipped_configs_validate():
         names.add(f.name)
         assert p.parallel.tensor_parallel * p.parallel.pipeline_parallel <= 8
     assert {"gpt-7b-b200x8-tp8-sp.toml", "gpt-7b-b200x8-zero3.toml", "gpt-13b-b200x8-tp4-pp2.toml", "gpt-125m-cpu-pp2.toml"} <= names
+
+
+def test_decode_staging_layout_and_buckets():
+    """The packed decode-step input buffer: int64 views stay 8-byte aligned, padding rows are inert, bucket sizes are
+    powers of two capped at the engine limits."""
+    import numpy as np
+    from llmctl_b200.serve.engine import InferenceEngine, _DecodeInputs
+    inp = _DecodeInputs(4, 6, torch.device("cpu"))
+    h = inp.host
+    h.fill_pad()
+    h.tokens[:2] = [11, 12]
+    h.slots[:2] = [100, 2 ** 33 + 5]           # slots are 64-bit
+    h.positions[:2] = [7, 8]
+    h.ctx[:2] = [8, 9]
+    h.block_tables[0, :3] = [5, 6, 7]
+    inp.upload()
+    assert inp.tokens.dtype == torch.int64 and inp.tokens.shape == (4, 1) and inp.tokens[:2, 0].tolist() == [11, 12]
+    assert inp.slots.tolist() == [100, 2 ** 33 + 5, -1, -1]
+    assert inp.positions.tolist() == [7, 8, 0, 0] and inp.ctx.tolist() == [8, 9, 0, 0]
+    assert inp.block_tables[0].tolist() == [5, 6, 7, 0, 0, 0] and int(inp.block_tables[1:].abs().sum()) == 0
+    assert inp.tokens.data_ptr() % 8 == 0 and inp.slots.data_ptr() % 8 == 0
+    assert inp.nbytes == (6 * 4 + 4 * 6) * 4
+    assert [InferenceEngine._bucket(n, 1, 8) for n in (1, 2, 3, 5, 8)] == [1, 2, 4, 8, 8]
+    assert InferenceEngine._bucket(300, 256, 4096) == 512 and InferenceEngine._bucket(5000, 256, 4096) == 5000
+    assert isinstance(h.tokens, np.ndarray)
+
+
+def test_paged_decode_split_heuristic():
+    from llmctl_b200.ops.serving import choose_splits
+    assert choose_splits(8, 4, 2304, 16) == 36             # 64-token splits, ~8 CTAs per SM
+    assert choose_splits(8, 32, 2304, 16) == 5             # enough (batch, head) pairs already
+    assert choose_splits(1, 4, 32768, 16) == 256           # capped
+    assert choose_splits(64, 32, 100, 16) == 1
+    assert choose_splits(1, 1, 10, 16) == 1
+
+
+def test_cpu_noops_for_gpu_only_facilities():
+    """NVTX ranges and the peer-signal watchdog must be inert (not failing) without a GPU."""
+    from llmctl_b200.comms import symm
+    from llmctl_b200.utils.nvtx import mark, nvtx_range
+    with nvtx_range("phase"):
+        mark("event")
+    if not torch.cuda.is_available():
+        assert symm.watchdog_poll() is None
+        symm.check_watchdog("unit test")
+    t = symm.PeerTable.of([0x1000, 0x2000])
+    assert t.ptr[0] == 0x1000 and t.ptr[1] == 0x2000 and not t.ptr[7]
