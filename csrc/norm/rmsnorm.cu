@@ -137,19 +137,45 @@ norm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __res
       if (kLayerNorm) dbacc[i][j] = 0.f;
     }
   }
+  // Software pipeline over this CTA's rows: the loads of row r+1 (dy, h) and the residual-gradient load of row r
+  // are issued before the block reduction of row r, so two rows of traffic are in flight per CTA instead of one
+  // load -> reduce -> load -> store chain per row (the kernel ran at 36% of HBM bandwidth when it was serial).
+  bf16x8 ndy[kVec], nh[kVec];
+  {
+    const int row0 = blockIdx.x;
+    if (row0 < rows) {
+      const size_t base0 = static_cast<size_t>(row0) * cols;
+#pragma unroll
+      for (int i = 0; i < kVec; ++i) {
+        const int v = i * 256 + threadIdx.x;
+        if (v < nvec) {
+          ndy[i] = load8(dy + base0 + v * 8);
+          nh[i] = load8(h + base0 + v * 8);
+        }
+      }
+    }
+  }
   for (int row = blockIdx.x; row < rows; row += gridDim.x) {
     const size_t base = static_cast<size_t>(row) * cols;
     const float rstd = rstd_in[row];
     const float mean = kLayerNorm ? mean_in[row] : 0.f;
     float g[kVec][8], xh[kVec][8];
+    bf16x8 rres[kVec];
     float c1 = 0.f, c2 = 0.f;
+    if (dres != nullptr) {
+#pragma unroll
+      for (int i = 0; i < kVec; ++i) {
+        const int v = i * 256 + threadIdx.x;
+        if (v < nvec) rres[i] = load8(dres + base + v * 8);
+      }
+    }
 #pragma unroll
     for (int i = 0; i < kVec; ++i) {
       const int v = i * 256 + threadIdx.x;
       if (v < nvec) {
         float d[8], a[8];
-        unpack8(load8(dy + base + v * 8), d);
-        unpack8(load8(h + base + v * 8), a);
+        unpack8(ndy[i], d);
+        unpack8(nh[i], a);
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           xh[i][j] = (a[j] - mean) * rstd;
@@ -158,6 +184,20 @@ norm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __res
           c2 += g[i][j];
           dwacc[i][j] += d[j] * xh[i][j];
           if (kLayerNorm) dbacc[i][j] += d[j];
+        }
+      }
+    }
+    {
+      const int nrow = row + gridDim.x;
+      if (nrow < rows) {
+        const size_t nbase = static_cast<size_t>(nrow) * cols;
+#pragma unroll
+        for (int i = 0; i < kVec; ++i) {
+          const int v = i * 256 + threadIdx.x;
+          if (v < nvec) {
+            ndy[i] = load8(dy + nbase + v * 8);
+            nh[i] = load8(h + nbase + v * 8);
+          }
         }
       }
     }
@@ -172,7 +212,7 @@ norm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __res
         for (int j = 0; j < 8; ++j) o[j] = rstd * (g[i][j] - xh[i][j] * c1 - c2);
         if (dres != nullptr) {
           float r[8];
-          unpack8(load8(dres + base + v * 8), r);
+          unpack8(rres[i], r);
 #pragma unroll
           for (int j = 0; j < 8; ++j) o[j] += r[j];
         }
