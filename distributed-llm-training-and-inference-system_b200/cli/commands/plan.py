@@ -18,7 +18,7 @@ from rich.table import Table
 
 from ...config.schemas import load_any
 from ...models.config import ModelConfig
-from ...partition.planner import HardwareNumbers, MeasuredCostModel, Plan, ReferenceCostModel
+from ...partition.planner import HardwareNumbers, MeasuredCostModel, ReferenceCostModel
 from ..common import console, fail, require
 
 app = typer.Typer(help="Compute parallelism and resource plans")

@@ -3,7 +3,6 @@
 from __future__ import annotations
 
 import json
-import sys
 from collections import defaultdict
 from pathlib import Path
 from typing import Optional

@@ -9,7 +9,6 @@ the global ``--seed/--deterministic/--log-level`` options propagate.
 from __future__ import annotations
 
 import json
-import sys
 from pathlib import Path
 from typing import Optional
 

@@ -13,7 +13,6 @@ SURVEY.md §2.4 last rows).
 """
 from __future__ import annotations
 
-import torch
 from torch.utils.checkpoint import checkpoint
 
 MODES = ("none", "selective", "full")

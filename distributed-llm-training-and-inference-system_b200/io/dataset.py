@@ -14,8 +14,6 @@ Reference: the reference's "dataset" is three hard-coded sentences x100 tokenise
 from __future__ import annotations
 
 import json
-import os
-import threading
 from dataclasses import dataclass
 from pathlib import Path
 from typing import Dict, Iterator, Optional, Tuple

@@ -14,7 +14,7 @@ reference configs/models/llama-7b.json and reference llmctl/cli/commands/init.py
 """
 from __future__ import annotations
 
-from typing import List, Optional, Tuple
+from typing import Optional, Tuple
 
 import torch
 import torch.nn as nn

@@ -14,7 +14,6 @@ can attribute speed-ups.
 """
 from __future__ import annotations
 
-import math
 from dataclasses import dataclass
 from typing import Optional, Tuple
 

@@ -10,7 +10,6 @@ Reference parity: the reference has no native layer.
 from __future__ import annotations
 
 import ctypes
-import os
 import threading
 from pathlib import Path
 from typing import Optional

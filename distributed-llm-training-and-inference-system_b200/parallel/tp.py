@@ -12,8 +12,6 @@ Reference: TP exists only as a planner integer (reference llmctl/cli/commands/pl
 """
 from __future__ import annotations
 
-import math
-from typing import Optional
 
 import torch
 import torch.distributed as dist

@@ -24,9 +24,8 @@ Reference: ZeRO exists only as the integer ``zero_stage`` (reference llmctl/cli/
 """
 from __future__ import annotations
 
-import math
 import warnings
-from typing import Callable, Dict, Iterable, List, Optional, Sequence
+from typing import Callable, Dict, List, Optional, Sequence
 
 import torch
 import torch.distributed as dist

@@ -10,7 +10,6 @@ import argparse
 import json
 import os
 import sys
-from dataclasses import fields
 from pathlib import Path
 
 _ROOT = Path(__file__).resolve().parents[2]

@@ -12,8 +12,6 @@ re-runs the HF model over the full sequences (``use_cache`` result discarded), s
 """
 from __future__ import annotations
 
-import json
-import math
 import threading
 import time
 from dataclasses import dataclass, field
