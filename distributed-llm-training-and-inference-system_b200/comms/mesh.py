@@ -89,7 +89,18 @@ def init_distributed(backend: Optional[str] = None, timeout_s: int = 1800) -> No
         local = int(os.environ.get("LOCAL_RANK", "0"))
         torch.cuda.set_device(local)
         kwargs["device_id"] = torch.device("cuda", local)
-    dist.init_process_group(backend=backend, timeout=datetime.timedelta(seconds=timeout_s), **kwargs)
+    timeout = datetime.timedelta(seconds=timeout_s)
+    restart = os.environ.get("TORCHELASTIC_RESTART_COUNT", "0")
+    if restart not in ("", "0") and os.environ.get("TORCHELASTIC_USE_AGENT_STORE", "").lower() in ("1", "true"):
+        # elastic restart: the agent's TCP store still holds the previous incarnation's rendezvous keys (the gloo
+        # full-mesh connect then dials a dead worker's address), so every incarnation gets its own key prefix
+        rank = int(os.environ["RANK"])
+        store = dist.TCPStore(os.environ["MASTER_ADDR"], int(os.environ["MASTER_PORT"]), world, is_master=False,
+                              timeout=timeout)
+        store = dist.PrefixStore(f"llmctl_restart_{restart}", store)
+        dist.init_process_group(backend=backend, store=store, rank=rank, world_size=world, timeout=timeout, **kwargs)
+        return
+    dist.init_process_group(backend=backend, timeout=timeout, **kwargs)
 
 
 def init_mesh(tp: int = 1, pp: int = 1, dp: Optional[int] = None, sequence_parallel: bool = False,

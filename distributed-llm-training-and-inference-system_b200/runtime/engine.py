@@ -323,6 +323,8 @@ class TrainingEngine:
             raise ValueError("--inject-fault expects rank:step:kind")
         if r != self.state.rank or s != self.global_step:
             return
+        if os.environ.get("TORCHELASTIC_RESTART_COUNT", "0") not in ("", "0"):
+            return                      # a drill fires once: the restarted job must be able to pass the same step
         if kind == "kill":
             os._exit(17)
         if kind == "hang":

@@ -73,7 +73,7 @@ class BaseLauncher(ABC):
         # complete checkpoint) instead of leaving the peers spinning; the flight recorder keeps the last collectives
         # of every rank for the post-mortem of a pipeline (batch_isend_irecv) hang
         env.setdefault("TORCH_NCCL_ASYNC_ERROR_HANDLING", "1")
-        env.setdefault("TORCH_NCCL_TRACE_BUFFER_SIZE", "2000")
+        env.setdefault("TORCH_FR_BUFFER_SIZE", "2000")
         env.setdefault("TORCH_NCCL_DUMP_ON_TIMEOUT", "1")
         if c.deterministic:
             env["PYTHONHASHSEED"] = str(c.seed)
@@ -84,6 +84,17 @@ class BaseLauncher(ABC):
     @abstractmethod
     def launch(self, script: str, script_args: List[str]) -> subprocess.Popen:
         ...
+
+
+def _die_with_parent():
+    """Child-side hook: own session (so Ctrl-C handling stays with the orchestrator) and SIGTERM when the process
+    that launched us dies — a killed CLI must not leave a torchrun tree behind."""
+    os.setsid()
+    try:
+        import ctypes
+        ctypes.CDLL("libc.so.6", use_errno=True).prctl(1, int(signal.SIGTERM))     # PR_SET_PDEATHSIG
+    except Exception:  # noqa: BLE001 - non-Linux or restricted: keep going without the safety net
+        pass
 
 
 class LocalLauncher(BaseLauncher):
@@ -99,7 +110,7 @@ class LocalLauncher(BaseLauncher):
     def launch(self, script, script_args):
         return subprocess.Popen(self.build_command(script, script_args), env=self.environment(),
                                 stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, bufsize=1,
-                                start_new_session=True)
+                                preexec_fn=_die_with_parent)
 
 
 class SlurmLauncher(BaseLauncher):

@@ -59,7 +59,11 @@ def main(argv=None) -> int:
     merged.pop("plan_path", None)
     cfg = create_training_config(**merged)
     if cfg.resume_from_checkpoint is None and os.environ.get("TORCHELASTIC_RESTART_COUNT", "0") not in ("", "0"):
-        cfg.resume_from_checkpoint = str(Path(cfg.output_dir) / "latest")   # elastic restart: auto-resume
+        # elastic restart: resume from the newest complete checkpoint — or from scratch if the job died before
+        # it wrote one
+        from llmctl_b200.io.checkpoint import latest_checkpoint
+        if latest_checkpoint(cfg.output_dir) is not None:
+            cfg.resume_from_checkpoint = str(Path(cfg.output_dir) / "latest")
     engine = TrainingEngine(cfg)
     result = engine.train()
     if engine.is_main:
