@@ -571,6 +571,15 @@ class ZeroOptimizer:
             u.exp_avg_sq.copy_(s["exp_avg_sq"])
             self._publish(u)
 
+    def republish_all(self) -> None:
+        """Rewrite every compute-precision parameter from the fp32 master weights (all ranks must call it).  Used
+        by the engine when a step produced non-finite values: the update was skipped, so the master copy is intact
+        and a corrupted compute copy is healed by this."""
+        with torch.no_grad():
+            for u in self.units:
+                self._publish(u)
+        PARAM_GENERATION[0] += 1
+
     def reset_from_params(self, step: int = 0) -> None:
         """Rebuild fp32 master weights from the current parameters and zero the moments (used when a
         checkpoint is resumed under a different plan, so the saved shards no longer line up)."""

@@ -84,7 +84,8 @@ class TrainingConfig:
     adam_eps: float = 1e-8
     total_steps: Optional[int] = None        # scheduler horizon (defaults to max_steps / epochs)
     async_checkpoint: bool = False
-    inject_fault: Optional[str] = None       # "rank:step:kind" with kind in kill|hang|nan  
+    inject_fault: Optional[str] = None
+    max_nonfinite_windows: int = 3       # consecutive non-finite logging windows before the run aborts (0 = never)       # "rank:step:kind" with kind in kill|hang|nan  
     metrics_jsonl: bool = True
     trace_schedule: Optional[str] = None     # e.g. "step(100)" (preset telemetry.profiling.schedule)
 
@@ -330,10 +331,11 @@ class TrainingEngine:
         if kind == "hang":
             time.sleep(3600)
         if kind == "nan":
+            # poison a weight every token goes through (a norm gain), not an embedding row that may be unused
             with torch.no_grad():
-                p = next(self.model.parameters())
-                if p.numel():
-                    p.view(-1)[0] = float("nan")
+                cands = [p for n, p in self.model.named_parameters() if "norm" in n and p.numel()]
+                p = cands[-1] if cands else next(self.model.parameters())
+                p.view(-1)[0] = float("nan")
 
     # ---- the loop ------------------------------------------------------------------------------------
     def train(self) -> Dict[str, Any]:
@@ -373,6 +375,7 @@ class TrainingEngine:
                 loss = self._reduce_scalar(out["loss"])
                 gn = float(out["grad_norm"])
                 self._check_comm_watchdog(f"steps up to {step}")
+                self._guard_nonfinite(step, loss, gn)
                 dt = (time.perf_counter() - window_t0) / max(window_steps, 1)
                 last = tracker.log(step, loss, gn, out["lr"], dt)
                 window_t0, window_steps = time.perf_counter(), 0
@@ -396,6 +399,23 @@ class TrainingEngine:
             self.metrics_file.close()
             self.metrics_file = None
         return {"global_step": self.global_step, **last}
+
+    def _guard_nonfinite(self, step: int, loss: float, grad_norm: float) -> None:
+        """Non-finite loss / gradient norm: the optimizer already skipped that update (the clip coefficient is NaN),
+        so the fp32 master weights are intact — re-publish them over the compute copies, and give up after
+        ``max_nonfinite_windows`` logging windows in a row instead of training (and checkpointing) garbage."""
+        if math.isfinite(loss) and math.isfinite(grad_norm):
+            self.nonfinite_windows = 0
+            return
+        self.nonfinite_windows = getattr(self, "nonfinite_windows", 0) + 1
+        if self.is_main:
+            self.logger.warning("step %d: non-finite loss/grad-norm (%s / %s): update skipped, parameters re-published "
+                                "from the fp32 master weights (%d in a row)", step, loss, grad_norm, self.nonfinite_windows)
+        self.optimizer.republish_all()
+        limit = getattr(self.config, "max_nonfinite_windows", 3)
+        if limit > 0 and self.nonfinite_windows >= limit:
+            raise RuntimeError(f"training diverged: {self.nonfinite_windows} consecutive logging windows with non-finite "
+                               f"loss or gradient norm (last at step {step}); no checkpoint is written from this state")
 
     def _check_comm_watchdog(self, context: str) -> None:
         """Peer-memory kernels give up (instead of hanging the GPU) when a peer's flag never arrives; whatever

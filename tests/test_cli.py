@@ -180,3 +180,18 @@ def _save_every(tmp_path, n):
     p = tmp_path / "preset.toml"
     p.write_text(f"[training]\nsave_interval = {n}\nlog_interval = 1\n")
     return p
+
+
+def test_nan_drill_heals_from_master_weights_and_aborts_when_persistent(tmp_path):
+    """A poisoned compute weight gives one non-finite step: the update is skipped, the parameters are re-published
+    from the fp32 master copy and training carries on with finite losses."""
+    out = tmp_path / "nan"
+    r = run("train", "launch", "--model", "gpt-tiny", "--output-dir", str(out), "--batch-size", "2", "--seq-len", "32",
+            "--max-steps", "5", "--mixed-precision", "fp32", "--distributed-backend", "gloo",
+            "--config", str(_save_every(tmp_path, 100)), "--inject-fault", "0:2:nan", timeout=300)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    rows = [json.loads(l) for l in (out / "metrics.jsonl").read_text().splitlines() if l.strip()]
+    losses = {row["step"]: row["loss"] for row in rows if "loss" in row}
+    assert losses[3] != losses[3] or losses[3] is None          # NaN at the poisoned step
+    assert all(losses[s] == losses[s] and losses[s] < 20 for s in (1, 2, 4, 5))
+    assert "re-published" in (r.stdout + r.stderr).replace("\n", " ") or "non-finite" in (r.stdout + r.stderr)
