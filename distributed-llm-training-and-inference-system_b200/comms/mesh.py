@@ -104,10 +104,10 @@ def init_distributed(backend: Optional[str] = None, timeout_s: int = 1800) -> No
 
 
 def init_mesh(tp: int = 1, pp: int = 1, dp: Optional[int] = None, sequence_parallel: bool = False,
-              zero_stage: int = 0, backend: Optional[str] = None) -> ParallelState:
+              zero_stage: int = 0, backend: Optional[str] = None, timeout_s: int = 1800) -> ParallelState:
     """Build the (pp, dp, tp) mesh over the default group and publish it as the global state."""
     global _STATE
-    init_distributed(backend)
+    init_distributed(backend, timeout_s=timeout_s)
     if dist.is_initialized():
         world, rank = dist.get_world_size(), dist.get_rank()
         bk = dist.get_backend()
@@ -131,24 +131,25 @@ def init_mesh(tp: int = 1, pp: int = 1, dp: Optional[int] = None, sequence_paral
     st.tp_rank = rank % tp
     st.dp_rank = (rank // tp) % dp
     st.pp_rank = rank // (tp * dp)
+    pg_timeout = datetime.timedelta(seconds=timeout_s)     # sub-groups do NOT inherit the default group's timeout
     if world > 1:
         # every rank must create every group, in the same order
         for p in range(pp):
             for d in range(dp):
                 ranks = [p * dp * tp + d * tp + t for t in range(tp)]
-                g = dist.new_group(ranks) if tp > 1 else None
+                g = dist.new_group(ranks, timeout=pg_timeout) if tp > 1 else None
                 if rank in ranks:
                     st.tp_group, st.tp_ranks = g, ranks
         for p in range(pp):
             for t in range(tp):
                 ranks = [p * dp * tp + d * tp + t for d in range(dp)]
-                g = dist.new_group(ranks) if dp > 1 else None
+                g = dist.new_group(ranks, timeout=pg_timeout) if dp > 1 else None
                 if rank in ranks:
                     st.dp_group, st.dp_ranks = g, ranks
         for d in range(dp):
             for t in range(tp):
                 ranks = [p * dp * tp + d * tp + t for p in range(pp)]
-                g = dist.new_group(ranks) if pp > 1 else None
+                g = dist.new_group(ranks, timeout=pg_timeout) if pp > 1 else None
                 if rank in ranks:
                     st.pp_group, st.pp_ranks = g, ranks
     _STATE = st

@@ -85,7 +85,8 @@ class TrainingConfig:
     total_steps: Optional[int] = None        # scheduler horizon (defaults to max_steps / epochs)
     async_checkpoint: bool = False
     inject_fault: Optional[str] = None
-    max_nonfinite_windows: int = 3       # consecutive non-finite logging windows before the run aborts (0 = never)       # "rank:step:kind" with kind in kill|hang|nan  
+    max_nonfinite_windows: int = 3       # consecutive non-finite logging windows before the run aborts (0 = never)
+    collective_timeout_s: int = 1800     # a collective that waits longer fails the rank (-> restart under --max-restarts)
     metrics_jsonl: bool = True
     trace_schedule: Optional[str] = None     # e.g. "step(100)" (preset telemetry.profiling.schedule)
 
@@ -186,7 +187,8 @@ class TrainingEngine:
             backend = "gloo"
         self.state: ParallelState = mesh_mod.init_mesh(tp=c.tensor_parallel, pp=c.pipeline_parallel,
                                                       sequence_parallel=c.sequence_parallel,
-                                                      zero_stage=c.zero_stage, backend=backend)
+                                                      zero_stage=c.zero_stage, backend=backend,
+                                                      timeout_s=c.collective_timeout_s)
         self._seed_everything()
         ops.set_backend(c.kernels)
         if c.deterministic:

@@ -195,3 +195,17 @@ def test_nan_drill_heals_from_master_weights_and_aborts_when_persistent(tmp_path
     assert losses[3] != losses[3] or losses[3] is None          # NaN at the poisoned step
     assert all(losses[s] == losses[s] and losses[s] < 20 for s in (1, 2, 4, 5))
     assert "re-published" in (r.stdout + r.stderr).replace("\n", " ") or "non-finite" in (r.stdout + r.stderr)
+
+
+def test_hang_drill_times_out_and_restarts(tmp_path):
+    """A rank that stops responding: the peers' collective gives up after --collective-timeout (sub-groups carry the
+    timeout too), the job is restarted and resumes from the newest checkpoint."""
+    out = tmp_path / "hang"
+    r = run("--seed", "3", "train", "launch", "--model", "gpt-tiny", "--output-dir", str(out), "--batch-size", "2", "--seq-len", "32",
+            "--max-steps", "6", "--mixed-precision", "fp32", "--distributed-backend", "gloo", "--gpus-per-node", "2",
+            "--zero-stage", "1", "--config", str(_save_every(tmp_path, 2)), "--max-restarts", "1", "--inject-fault", "1:3:hang",
+            "--collective-timeout", "10", timeout=420)
+    assert r.returncode == 0, r.stdout[-2500:] + r.stderr[-2500:]
+    st = json.loads((out / "final" / "training_state.json").read_text())
+    assert st["global_step"] == 6
+    assert "resumed from" in (r.stdout + r.stderr).replace("\n", " ")
