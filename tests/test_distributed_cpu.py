@@ -144,3 +144,21 @@ def test_optimizer_state_resharded_when_dp_changes(tmp_path):
     out = eng.train_step()
     assert torch.isfinite(out["loss"]).all()
     mesh.reset_state()
+
+
+CONFIGS_W4 = {
+    "tp2_pp2": dict(tensor_parallel=2, pipeline_parallel=2, batch_size=2, gradient_accumulation_steps=2),
+    "dp2_tp2_sp_zero3": dict(tensor_parallel=2, sequence_parallel=True, zero_stage=3, batch_size=2),
+}
+
+
+@pytest.mark.slow
+@pytest.mark.parametrize("name", list(CONFIGS_W4))
+def test_loss_parity_world4_combined_modes(name, tmp_path):
+    """Three-axis mesh arithmetic (pp x dp x tp rank layout, group creation order) at world = 4."""
+    full_path = str(tmp_path / "full.pt")
+    ref = _reference(full_path, 4)
+    res = run_distributed(_worker, 4, full_path, CONFIGS_W4[name], 4, timeout=400)
+    for r in res:
+        for a, b in zip(r, ref):
+            assert abs(a - b) < 2e-3 * max(1.0, abs(b)), f"{name}: {r} vs single-process {ref}"
