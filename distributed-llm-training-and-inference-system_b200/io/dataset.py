@@ -14,6 +14,7 @@ Reference: the reference's "dataset" is three hard-coded sentences x100 tokenise
 from __future__ import annotations
 
 import json
+import os
 from dataclasses import dataclass
 from pathlib import Path
 from typing import Dict, Iterator, Optional, Tuple
@@ -171,22 +172,68 @@ class TokenLoader:
         self._next = None
 
 
+def _token_file_for(src: Path, vocab_size: int) -> Path:
+    """Tokenise a ``.txt`` / ``.jsonl`` source once (byte-level tokenizer unless the file sits next to an HF tokenizer)
+    and cache the flat token file beside it; re-used while it is newer than the source."""
+    from ..serve.tokenizer import load_tokenizer
+    dst = src.with_suffix(src.suffix + f".v{vocab_size}.bin")
+    if not dst.exists() or dst.stat().st_mtime < src.stat().st_mtime:
+        tok = load_tokenizer(str(src.parent), vocab_size)
+        tmp = dst.with_name(dst.name + f".tmp{os.getpid()}")          # every rank may get here at once: build privately,
+        build_token_file(src, tmp, tok, dtype="uint16" if tok.vocab_size <= 65536 else "uint32")
+        meta_tmp = tmp.with_suffix(tmp.suffix + ".meta.json")
+        os.replace(meta_tmp, dst.with_suffix(dst.suffix + ".meta.json"))
+        os.replace(tmp, dst)                                           # then publish atomically
+    return dst
+
+
+def _dataset_from_path(sp: Path, vocab_size: int, seq_len: int):
+    if sp.suffix == ".bin":
+        return MMapTokenDataset(sp, seq_len)
+    if sp.suffix in (".txt", ".jsonl"):
+        return MMapTokenDataset(_token_file_for(sp, vocab_size), seq_len)
+    raise ValueError(f"unsupported dataset file {sp} (expected a token .bin, a .txt or a .jsonl with a 'text' field)")
+
+
 def build_dataset(spec: Optional[str], vocab_size: int, seq_len: int, seed: int = 1234):
-    """``None`` / ``"synthetic"`` -> synthetic stream; a path to a token ``.bin`` -> mmap dataset; a data
-    TOML (reference llmctl/cli/commands/init.py:166-184 schema) -> its first train source."""
+    """``None`` / ``"synthetic"`` -> synthetic stream; a token ``.bin`` -> mmap dataset; a ``.txt`` / ``.jsonl`` file ->
+    tokenised once into a cached ``.bin``; a data TOML -> its first train source (``[[sources]]`` of the reference
+    schema, reference llmctl/cli/commands/init.py:166-184, or a ``[dataset]`` table with ``type`` / ``path``).
+    A source that was named but cannot be used is an error — never a silent fall-back to random tokens."""
     if spec in (None, "", "synthetic"):
         return SyntheticTokenDataset(vocab_size, seq_len, seed=seed)
     p = Path(spec)
-    if p.suffix == ".toml" and p.exists():
+    if p.suffix == ".toml":
+        if not p.exists():
+            raise FileNotFoundError(f"data config not found: {p}")
         import tomllib
         cfg = tomllib.loads(p.read_text())
-        for src in cfg.get("sources", []):
-            sp = Path(src.get("path", ""))
+        ds = cfg.get("dataset")
+        if isinstance(ds, dict):
+            if ds.get("type", "synthetic") == "synthetic":
+                return SyntheticTokenDataset(vocab_size, seq_len, seed=int(ds.get("seed", seed)))
+            sp = Path(str(ds.get("path", "")))
             if not sp.is_absolute():
-                sp = p.parent.parent.parent / sp if not sp.exists() else sp
-            if src.get("split", "train") == "train" and sp.suffix == ".bin" and sp.exists():
-                return MMapTokenDataset(sp, seq_len)
+                sp = (p.parent / sp) if (p.parent / sp).exists() else sp
+            if not sp.exists():
+                raise FileNotFoundError(f"{p}: dataset path {ds.get('path')!r} does not exist")
+            return _dataset_from_path(sp, vocab_size, seq_len)
+        missing = []
+        for src in cfg.get("sources", []):
+            if src.get("split", "train") != "train":
+                continue
+            raw = Path(src.get("path", ""))
+            cands = [raw] if raw.is_absolute() else [raw, p.parent / raw, p.parent.parent / raw, p.parent.parent.parent / raw]
+            sp = next((c for c in cands if c.exists()), None)
+            if sp is None:
+                missing.append(str(raw))
+                continue
+            return _dataset_from_path(sp, vocab_size, seq_len)
+        if missing:
+            # the scaffold ships a data TOML that points at files the user has not created yet
+            import warnings
+            warnings.warn(f"{p}: train source(s) {missing} not found — using the synthetic token stream")
         return SyntheticTokenDataset(vocab_size, seq_len, seed=seed)
-    if p.exists() and p.suffix == ".bin":
-        return MMapTokenDataset(p, seq_len)
-    return SyntheticTokenDataset(vocab_size, seq_len, seed=seed)
+    if not p.exists():
+        raise FileNotFoundError(f"dataset {p} does not exist (use 'synthetic', a token .bin, a .txt/.jsonl file or a data TOML)")
+    return _dataset_from_path(p, vocab_size, seq_len)

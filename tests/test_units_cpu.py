@@ -265,3 +265,25 @@ def test_cpu_noops_for_gpu_only_facilities():
         symm.check_watchdog("unit test")
     t = symm.PeerTable.of([0x1000, 0x2000])
     assert t.ptr[0] == 0x1000 and t.ptr[1] == 0x2000 and not t.ptr[7]
+
+
+def test_text_dataset_is_tokenised_and_missing_sources_fail(tmp_path):
+    from llmctl_b200.io.dataset import MMapTokenDataset, SyntheticTokenDataset, build_dataset
+    txt = tmp_path / "corpus.txt"
+    txt.write_text("the quick brown fox jumps over the lazy dog\n" * 50)
+    ds = build_dataset(str(txt), 512, 16)
+    assert isinstance(ds, MMapTokenDataset) and len(ds) > 10
+    assert (tmp_path / "corpus.txt.v512.bin").exists()
+    toml = tmp_path / "data.toml"
+    toml.write_text(f'[dataset]\ntype = "text"\npath = "{txt}"\n')
+    assert isinstance(build_dataset(str(toml), 512, 16), MMapTokenDataset)
+    toml.write_text('[[sources]]\npath = "corpus.txt"\nsplit = "train"\n')
+    assert isinstance(build_dataset(str(toml), 512, 16), MMapTokenDataset)
+    toml.write_text('[dataset]\ntype = "synthetic"\n')
+    assert isinstance(build_dataset(str(toml), 512, 16), SyntheticTokenDataset)
+    import pytest
+    with pytest.raises(FileNotFoundError):
+        build_dataset(str(tmp_path / "nope.bin"), 512, 16)
+    toml.write_text('[dataset]\ntype = "tokens"\npath = "missing.bin"\n')
+    with pytest.raises(FileNotFoundError):
+        build_dataset(str(toml), 512, 16)
