@@ -67,6 +67,8 @@ def load_tokenizer(path_or_name: Optional[str], vocab_size: int = 32000):
             try:
                 from transformers import AutoTokenizer
                 return _HFWrapper(AutoTokenizer.from_pretrained(str(p), local_files_only=True))
-            except Exception:  # noqa: BLE001 - fall back to bytes rather than fail to serve
-                pass
+            except Exception as exc:  # noqa: BLE001 - keep serving, but say that the vocabulary is no longer the model's
+                import warnings
+                warnings.warn(f"tokenizer files in {p} could not be loaded ({type(exc).__name__}: {exc}); using the "
+                              f"byte-level tokenizer — token ids will not match a model trained with that tokenizer")
     return ByteTokenizer(vocab_size)
