@@ -202,6 +202,24 @@ def latest_checkpoint(output_dir: str | Path) -> Optional[Path]:
     return cks[-1] if cks else None
 
 
+def _step_of(ckpt: Path) -> int:
+    try:
+        return int(json.loads((ckpt / "training_state.json").read_text()).get("global_step", -1))
+    except (OSError, ValueError):
+        return -1
+
+
+def newest_state(output_dir: str | Path) -> Optional[Path]:
+    """The most advanced complete state under ``output_dir``: the ``latest`` periodic checkpoint, or ``final/`` when
+    the run ended after it (an extended run should continue from where the previous one stopped)."""
+    root = Path(output_dir)
+    best = latest_checkpoint(root)
+    fin = root / "final"
+    if (fin / "COMPLETE").exists() and (best is None or _step_of(fin) >= _step_of(best)):
+        best = fin
+    return best
+
+
 def gc_checkpoints(output_dir: str | Path, keep_latest: int, dry_run: bool = False) -> List[Path]:
     """Delete all but the newest ``keep_latest`` complete checkpoints, plus any incomplete ones that are
     older than the newest complete one (``llmctl admin gc``; reference llmctl/cli/commands/admin.py:9-13 stub)."""

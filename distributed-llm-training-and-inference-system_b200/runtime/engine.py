@@ -487,12 +487,17 @@ class TrainingEngine:
     def load_checkpoint(self, checkpoint_path: str):
         p = Path(checkpoint_path)
         if p.name in ("latest", "auto") or (p.is_dir() and not (p / "training_state.json").exists()):
-            root = p.parent if p.name in ("latest", "auto") else p
-            found = ckpt_io.latest_checkpoint(root)
+            if str(p) in ("latest", "auto"):
+                root = Path(self.config.output_dir)          # the bare word means "of this run's output directory"
+            else:
+                root = p.parent if p.name in ("latest", "auto") else p
+            found = ckpt_io.newest_state(root)
             if found is None:
-                if self.is_main:
-                    self.logger.warning("no complete checkpoint under %s; starting fresh", root)
-                return None
+                if p.name == "auto":                        # "auto": resume if there is something to resume
+                    if self.is_main:
+                        self.logger.warning("no complete checkpoint under %s; starting fresh", root)
+                    return None
+                raise FileNotFoundError(f"--checkpoint {checkpoint_path}: no complete checkpoint under {root}")
             p = found
         tstate = ckpt_io.load_checkpoint(p, self.model, self.optimizer)
         self.global_step = int(tstate.get("global_step", 0))

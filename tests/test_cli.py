@@ -209,3 +209,19 @@ def test_hang_drill_times_out_and_restarts(tmp_path):
     st = json.loads((out / "final" / "training_state.json").read_text())
     assert st["global_step"] == 6
     assert "resumed from" in (r.stdout + r.stderr).replace("\n", " ")
+
+
+def test_checkpoint_latest_resumes_from_this_runs_output_dir(tmp_path):
+    """`--checkpoint latest` means the newest complete state of --output-dir (periodic checkpoint or final/), and is an
+    error — not a silent fresh start — when there is nothing to resume."""
+    out = tmp_path / "run"
+    common = ["train", "launch", "--model", "gpt-tiny", "--output-dir", str(out), "--batch-size", "2", "--seq-len", "32",
+              "--mixed-precision", "fp32", "--distributed-backend", "gloo", "--config", str(_save_every(tmp_path, 2))]
+    r = run(*common, "--checkpoint", "latest", "--max-steps", "2", timeout=300)
+    assert r.returncode != 0 and "no complete checkpoint" in (r.stdout + r.stderr).replace("\n", " ")
+    assert run(*common, "--max-steps", "5", timeout=300).returncode == 0
+    r = run(*common, "--checkpoint", "latest", "--max-steps", "7", timeout=300)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    text = (r.stdout + r.stderr).replace("\n", " ")
+    assert "resumed from" in text and "at step 5" in text              # final/ (step 5) beats checkpoint-4
+    assert json.loads((out / "final" / "training_state.json").read_text())["global_step"] == 7
