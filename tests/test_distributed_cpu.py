@@ -162,3 +162,15 @@ def test_loss_parity_world4_combined_modes(name, tmp_path):
     for r in res:
         for a, b in zip(r, ref):
             assert abs(a - b) < 2e-3 * max(1.0, abs(b)), f"{name}: {r} vs single-process {ref}"
+
+
+@pytest.mark.parametrize("mode", ["selective", "full"])
+def test_activation_checkpoint_modes_do_not_change_the_trajectory(mode, tmp_path):
+    from llmctl_b200.comms import mesh
+    full_path = str(tmp_path / "full.pt")
+    ref = _reference(full_path, 4)
+    mesh.reset_state()
+    eng = _make_engine(str(tmp_path / mode), batch_size=4, activation_checkpoint=mode)
+    out = _run(eng, torch.load(full_path), 4)
+    mesh.reset_state()
+    assert all(abs(a - b) < 1e-4 for a, b in zip(out, ref)), (mode, out, ref)
