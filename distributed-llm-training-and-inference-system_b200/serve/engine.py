@@ -77,6 +77,7 @@ class Sequence:
     created: float = field(default_factory=time.time)
     first_token_time: Optional[float] = None
     on_token: Optional[object] = None      # callback(seq, token) for streaming
+    cancel_requested: bool = False         # set from any thread (client went away); honoured at the next token
     done_event: threading.Event = field(default_factory=threading.Event)
 
     @property
@@ -493,7 +494,9 @@ class InferenceEngine:
             except Exception:  # noqa: BLE001 - a broken stream consumer must not kill the engine
                 pass
         eos = getattr(self.tokenizer, "eos_token_id", None)
-        if eos is not None and tok == eos:
+        if s.cancel_requested:
+            s.finish_reason = "cancelled"          # frees the KV blocks and the batch slot right away
+        elif eos is not None and tok == eos:
             s.finish_reason = "stop"
         elif len(s.generated) >= s.max_tokens:
             s.finish_reason = "length"

@@ -173,6 +173,8 @@ class InferenceServer:
                 self.errors += 1
             return self._response(rid, seq, n_prompt)
         finally:
+            if not seq.finished:
+                seq.cancel_requested = True
             self.active_requests.pop(rid, None)
 
     async def _stream(self, req: GenerationRequest):
@@ -199,6 +201,8 @@ class InferenceServer:
             yield "data: [DONE]\n\n"
             self.completed += 1
         finally:
+            if not seq.finished:
+                seq.cancel_requested = True        # client disconnected: stop generating for it
             self.active_requests.pop(rid, None)
 
     # ---- lifecycle -----------------------------------------------------------------------------------------

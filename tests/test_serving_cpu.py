@@ -165,3 +165,17 @@ def test_http_api_contract():
         assert c.post("/v1/completions", json={"prompt": "x", "max_tokens": 0}).status_code == 422
     finally:
         srv.shutdown()
+
+
+def test_cancelled_sequence_frees_its_blocks_early():
+    eng = _tiny_engine(max_batch_size=2, max_batch_tokens=256)
+    a = eng.add_request([5, 6, 7], max_tokens=50, temperature=0.0)
+    b = eng.add_request([8, 9], max_tokens=6, temperature=0.0)
+    eng.step(); eng.step()
+    a.cancel_requested = True
+    steps = 0
+    while eng.has_work():
+        eng.step(); steps += 1
+    assert a.finished and a.finish_reason == "cancelled" and len(a.generated) < 10
+    assert b.finish_reason == "length" and len(b.generated) == 6
+    assert eng.kv.free_blocks == 64 and steps < 12
