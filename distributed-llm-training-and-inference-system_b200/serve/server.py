@@ -100,6 +100,13 @@ class InferenceServer:
         self.errors = 0
         self.loop_thread = EngineLoop(self.engine)
         self.loop_thread.on_finished = self._record
+        try:
+            # register the llmctl_inference_* metrics in the default registry: GET /metrics serves them from this
+            # process, no second HTTP server is started
+            from ..metrics.observability import get_observability_manager
+            get_observability_manager().enable_prometheus(port=None)
+        except Exception:  # noqa: BLE001 - metrics are optional (prometheus_client missing)
+            pass
         self.started = time.time()
         self.app = FastAPI(title="llmctl inference server", version="0.1.0")
         self.app.add_middleware(CORSMiddleware, allow_origins=["*"], allow_credentials=True, allow_methods=["*"],

@@ -163,6 +163,10 @@ def test_http_api_contract():
             lines = [l for l in s.iter_lines() if l.startswith("data: ")]
         assert lines[-1] == "data: [DONE]" and len(lines) >= 3
         assert c.post("/v1/completions", json={"prompt": "x", "max_tokens": 0}).status_code == 422
+        import time as _t
+        _t.sleep(0.2)                                    # the engine loop records finished requests
+        m = c.get("/metrics").text
+        assert 'llmctl_inference_requests_total{status="ok"}' in m and "llmctl_inference_latency_seconds_count" in m
     finally:
         srv.shutdown()
 
