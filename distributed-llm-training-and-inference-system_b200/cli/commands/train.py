@@ -49,6 +49,7 @@ def launch(
     max_restarts: int = typer.Option(0, "--max-restarts", help="Elastic restarts with auto-resume"),
     inject_fault: Optional[str] = typer.Option(None, "--inject-fault", help="debug: rank:step:kill|hang|nan"),
     collective_timeout: Optional[int] = typer.Option(None, "--collective-timeout", help="Seconds a collective may wait before the rank fails (default 1800)"),
+    prometheus_port: Optional[int] = typer.Option(None, "--prometheus-port", help="Rank 0 serves llmctl_training_* metrics on this port"),
     dry_run: bool = typer.Option(False, "--dry-run", help="Show the resolved launch, start nothing"),
 ):
     """Launch a training run."""
@@ -68,6 +69,7 @@ def launch(
              "tensor_parallel": tensor_parallel, "pipeline_parallel": pipeline_parallel, "zero_stage": zero_stage,
              "activation_checkpoint": activation_checkpoint, "kernels": kernels, "distributed_backend": backend,
              "resume_from_checkpoint": str(checkpoint) if checkpoint else None, "inject_fault": inject_fault, "collective_timeout_s": collective_timeout,
+             "prometheus_port": prometheus_port, "otlp_endpoint": g.otlp_endpoint,
              "seed": g.explicit.get("seed"), "log_level": g.explicit.get("log_level")}
     argv = []
     if config:

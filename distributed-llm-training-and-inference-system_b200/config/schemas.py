@@ -196,6 +196,7 @@ class TrainingSection(_Base):
 
 class TelemetrySection(_Base):
     otlp_endpoint: Optional[str] = None
+    prometheus_port: Optional[int] = None      # rank 0 serves the llmctl_training_* / llmctl_system_* metrics here
     metrics: List[str] = []
     traces: bool = False
     profiling: Dict[str, Any] = {}
@@ -317,6 +318,10 @@ def resolve_training_config(preset: Optional[Union[str, Path]] = None, plan: Opt
                        logging_steps=t.log_interval, gradient_clipping=t.gradient_clipping,
                        mixed_precision=t.mixed_precision)
             out.update(save_total_limit=ps.checkpoint.keep_latest, async_checkpoint=ps.checkpoint.async_)
+            if ps.telemetry.prometheus_port:
+                out["prometheus_port"] = ps.telemetry.prometheus_port
+            if ps.telemetry.otlp_endpoint:
+                out["otlp_endpoint"] = ps.telemetry.otlp_endpoint
             prof = ps.telemetry.profiling or {}
             if prof.get("enable"):
                 out["trace_schedule"] = prof.get("schedule", "step(100)")

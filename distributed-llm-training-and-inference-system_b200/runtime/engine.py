@@ -89,6 +89,8 @@ class TrainingConfig:
     collective_timeout_s: int = 1800     # a collective that waits longer fails the rank (-> restart under --max-restarts)
     metrics_jsonl: bool = True
     trace_schedule: Optional[str] = None     # e.g. "step(100)" (preset telemetry.profiling.schedule)
+    prometheus_port: Optional[int] = None    # rank 0: Prometheus endpoint with the reference's metric names
+    otlp_endpoint: Optional[str] = None      # OTLP/HTTP collector for spans + metrics
 
     def to_dict(self) -> Dict[str, Any]:
         d = asdict(self)
@@ -361,6 +363,14 @@ class TrainingEngine:
         total_steps = c.max_steps if c.max_steps > 0 else c.num_epochs * c.steps_per_epoch
         tokens_per_step = c.batch_size * c.seq_len * st.dp * c.gradient_accumulation_steps
         from ..metrics import hooks as mhooks
+        if self.is_main and (c.prometheus_port or c.otlp_endpoint):
+            from ..metrics.observability import get_observability_manager, setup_observability
+            if c.otlp_endpoint:
+                setup_observability(prometheus_port=c.prometheus_port, otlp_endpoint=c.otlp_endpoint, start_sampler=True)
+            else:
+                mgr = get_observability_manager()
+                mgr.enable_prometheus(c.prometheus_port)
+                mgr.start()                               # system sampler + gauge refresh thread
         tracker = mhooks.TrainingTracker(self, tokens_per_step)
         profiler = mhooks.make_profiler(c.trace_schedule, out_dir / "trace", st.rank) if c.trace_schedule else None
         last = {}

@@ -38,7 +38,8 @@ def parse_args(argv=None):
                   "resume_from_checkpoint": str, "logging_steps": int, "log_level": str, "seed": int,
                   "seq_len": int, "tensor_parallel": int, "pipeline_parallel": int, "zero_stage": int,
                   "activation_checkpoint": str, "kernels": str, "steps_per_epoch": int, "inject_fault": str,
-                  "trace_schedule": str, "total_steps": int, "collective_timeout_s": int, "max_nonfinite_windows": int}
+                  "trace_schedule": str, "total_steps": int, "collective_timeout_s": int, "max_nonfinite_windows": int,
+                  "prometheus_port": int, "otlp_endpoint": str}
     for name, tp in flag_types.items():
         ap.add_argument("--" + name.replace("_", "-"), dest=name, type=tp, default=None)
     ap.add_argument("--deterministic", action="store_true", default=None)
