@@ -4,6 +4,7 @@ window only."""
 from __future__ import annotations
 
 import json
+import math
 import time
 from pathlib import Path
 from typing import Any, Dict, Optional
@@ -27,6 +28,14 @@ class TrainingTracker:
         try:
             from .health import get_health_manager
             self._health = get_health_manager()
+            if engine.is_main and not getattr(self._health, "_llmctl_wired", False):
+                # monitors run for the life of the run; alerts go to the run's log (stall, non-finite loss, gradient
+                # norm out of range, memory / disk pressure)
+                log = engine.logger
+                self._health.add_alert_callback(
+                    lambda r: log.warning("health %s: %s - %s", r.status.value.upper(), r.component, r.message))
+                self._health.start_monitoring()
+                self._health._llmctl_wired = True
         except Exception:  # noqa: BLE001
             self._health = None
 
@@ -50,6 +59,8 @@ class TrainingTracker:
                                            grad_norm=grad_norm, step_time=step_time, flops=flops, mfu=mfu)
         if self._health is not None:
             self._health.update_training_metrics(step=step, loss=loss, grad_norm=grad_norm)
+            if e.is_main and not (math.isfinite(loss) and math.isfinite(grad_norm)):
+                self._health._perform_health_checks()          # do not wait for the next periodic check
         return rec
 
 
