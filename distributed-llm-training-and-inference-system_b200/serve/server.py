@@ -216,6 +216,19 @@ class InferenceServer:
     def start_background(self) -> None:
         if not self.loop_thread.is_alive():
             self.loop_thread.start()
+        try:
+            # error rate / latency / queue depth monitors (fed by _record) raise alerts in the server log
+            import logging
+            from ..metrics.health import get_health_manager
+            hm = get_health_manager()
+            if not getattr(hm, "_llmctl_serve_wired", False):
+                log = logging.getLogger("llmctl.serve")
+                hm.add_alert_callback(lambda r: log.warning("health %s: %s - %s", r.status.value.upper(), r.component, r.message)
+                                      if r.component != "training" else None)
+                hm.start_monitoring()
+                hm._llmctl_serve_wired = True
+        except Exception:  # noqa: BLE001 - monitoring is best effort
+            pass
 
     async def start_server(self):
         import uvicorn
