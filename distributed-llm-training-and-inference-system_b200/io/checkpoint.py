@@ -84,10 +84,17 @@ class _AsyncWriter:
 
 
 _writer = _AsyncWriter()
+_pending_commit = None      # multi-rank async save: callable that publishes the checkpoint once every rank has written
 
 
 def wait_for_async_save() -> None:
+    """Join this rank's background write; with several ranks also commit the pending checkpoint (collective: every
+    rank calls this at the same point — the next save, or the end of training)."""
+    global _pending_commit
     _writer.wait()
+    if _pending_commit is not None:
+        commit, _pending_commit = _pending_commit, None
+        commit()
 
 
 def save_checkpoint(output_dir: str | Path, step: int, model: torch.nn.Module, optimizer=None, *,
@@ -98,6 +105,7 @@ def save_checkpoint(output_dir: str | Path, step: int, model: torch.nn.Module, o
     from safetensors.torch import save_file
 
     st = get_state()
+    wait_for_async_save()                 # the previous asynchronous save is finished (and committed) first
     ckpt = checkpoint_dir(output_dir, step, final)
     if st.rank == 0:
         if ckpt.exists() and (ckpt / "COMPLETE").exists():
@@ -153,6 +161,18 @@ def save_checkpoint(output_dir: str | Path, step: int, model: torch.nn.Module, o
                          "shards": [f"model-tp{t:02d}-pp{p:02d}.safetensors" for p in range(st.pp) for t in range(st.tp)]}
                 (ckpt / "model.safetensors.index.json").write_text(json.dumps(index, indent=2))
 
+    def commit():
+        if dist.is_initialized():
+            dist.barrier()                # every rank's files are on disk
+        if st.rank == 0:
+            (ckpt / "COMPLETE").write_text(str(step))
+            if not final:
+                tmp = Path(output_dir) / ".latest.tmp"
+                tmp.write_text(ckpt.name)
+                os.replace(tmp, Path(output_dir) / "latest")
+            if keep_latest:
+                gc_checkpoints(output_dir, keep_latest)
+
     def finish():
         write()
         if dist.is_initialized() and not async_write:
@@ -166,8 +186,14 @@ def save_checkpoint(output_dir: str | Path, step: int, model: torch.nn.Module, o
             if keep_latest:
                 gc_checkpoints(output_dir, keep_latest)
 
+    global _pending_commit
     if async_write and st.world_size == 1:
         _writer.submit(finish)
+    elif async_write and not final:
+        # several ranks: each writes its own files in the background; the COMPLETE marker (which needs all of them)
+        # is committed at the next synchronisation point — the next save or the end of training
+        _writer.submit(write)
+        _pending_commit = commit
     else:
         finish()
         _barrier()

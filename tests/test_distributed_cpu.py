@@ -174,3 +174,23 @@ def test_activation_checkpoint_modes_do_not_change_the_trajectory(mode, tmp_path
     out = _run(eng, torch.load(full_path), 4)
     mesh.reset_state()
     assert all(abs(a - b) < 1e-4 for a, b in zip(out, ref)), (mode, out, ref)
+
+
+def _async_ckpt_worker(rank, world, out_dir):
+    eng = _make_engine(out_dir, zero_stage=1, batch_size=2, max_steps=5, save_steps=2, async_checkpoint=True)
+    eng.prepare_datasets()
+    eng.setup_optimizer_and_scheduler()
+    res = eng.train()
+    return res["loss"]
+
+
+def test_async_checkpoints_with_two_ranks_commit_at_next_sync_point(tmp_path):
+    """Each rank writes its shard in the background; COMPLETE / latest appear once every rank's files are on disk."""
+    import json
+    losses = run_distributed(_async_ckpt_worker, 2, str(tmp_path))
+    assert losses[0] == pytest.approx(losses[1])
+    for step in (2, 4):
+        d = tmp_path / f"checkpoint-{step}"
+        assert (d / "COMPLETE").exists() and (d / "optim" / "rank-00001.pt").exists() and (d / "model.safetensors").exists()
+    assert (tmp_path / "latest").read_text().strip() == "checkpoint-4"
+    assert json.loads((tmp_path / "final" / "training_state.json").read_text())["global_step"] == 5
