@@ -389,6 +389,11 @@ class TrainingEngine:
                 self._check_comm_watchdog(f"steps up to {step}")
                 self._guard_nonfinite(step, loss, gn)
                 dt = (time.perf_counter() - window_t0) / max(window_steps, 1)
+                if st.world_size > 1:
+                    # the slowest rank defines the step time (and tokens/s, MFU) that gets reported
+                    tmax = torch.tensor([dt], dtype=torch.float64, device=st.device)
+                    dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+                    dt = float(tmax.item())
                 last = tracker.log(step, loss, gn, out["lr"], dt)
                 window_t0, window_steps = time.perf_counter(), 0
             if c.eval_steps > 0 and step % c.eval_steps == 0:
