@@ -118,6 +118,11 @@ class GPTModel(nn.Module):
         self.layer_lo, self.layer_hi = lo, hi
         self.is_first = lo == 0
         self.is_last = hi == cfg.layers
+        if cfg.tie_word_embeddings and not (self.is_first and self.is_last):
+            # embedding (first stage) and output head (last stage) would be two copies that need a weight broadcast
+            # at start-up and a gradient sum every step; not built — fail here rather than train them untied
+            raise ValueError("tie_word_embeddings=true is not supported with pipeline_parallel > 1: the tied matrix "
+                             "would live on two stages; use pipeline_parallel=1 or untie the embeddings")
         self.activation_checkpoint = activation_checkpoint
         self.vocab_padded = _pad_vocab(cfg.vocab_size, st.tp)
         if self.is_first:
@@ -130,6 +135,7 @@ class GPTModel(nn.Module):
             self.final_norm = Norm(cfg, dtype, device)
             if cfg.tie_word_embeddings and self.is_first:
                 self.lm_head = None
+                self.embed.weight._zero3_keep_through_forward = True    # used again by head() in the same forward
             else:
                 self.lm_head = tpl.ColumnParallelLinear(cfg.hidden, self.vocab_padded, std=cfg.init_std,
                                                         dtype=dtype, device=device, fused_name="lm_head")

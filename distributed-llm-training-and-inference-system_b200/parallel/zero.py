@@ -309,6 +309,10 @@ class ZeroOptimizer:
                 u.module.register_forward_hook(lambda m, a, o, u=u: self._post_forward(u))
 
     def _post_forward(self, u: ParamUnit) -> None:
+        # a unit whose weight is used again later in the same forward (tied embedding -> output head) stays gathered
+        # until its gradients are complete (_unit_ready) — releasing it here would hand the head an empty tensor
+        if any(getattr(p, "_zero3_keep_through_forward", False) for p in u.params):
+            return
         # keep the parameters while a checkpointed recompute is inside backward (freed by _unit_ready)
         if not torch.is_grad_enabled() or not getattr(self, "_in_backward", False):
             u.release_params()

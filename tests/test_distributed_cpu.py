@@ -59,6 +59,11 @@ def _worker(rank, world, full_path, kw, global_batch):
         return _run(eng, full, global_batch)
 
 
+def _worker_v(rank, world, full_path, kw, global_batch, model_extra):
+    MODEL.update(model_extra)
+    return _worker(rank, world, full_path, kw, global_batch)
+
+
 CONFIGS = {
     "pp2_zero1": dict(pipeline_parallel=2, zero_stage=1, batch_size=2, gradient_accumulation_steps=2),
     "dp2_zero0": dict(zero_stage=0, batch_size=2),
@@ -194,3 +199,22 @@ def test_async_checkpoints_with_two_ranks_commit_at_next_sync_point(tmp_path):
         assert (d / "COMPLETE").exists() and (d / "optim" / "rank-00001.pt").exists() and (d / "model.safetensors").exists()
     assert (tmp_path / "latest").read_text().strip() == "checkpoint-4"
     assert json.loads((tmp_path / "final" / "training_state.json").read_text())["global_step"] == 5
+
+
+def test_tied_embeddings_under_zero3_and_rejected_across_pipeline_stages(tmp_path):
+    """LayerNorm + GELU + tied output head: ZeRO-3 must keep the tied matrix gathered until the head has used it
+    (it used to hand the head an empty tensor); tying across pipeline stages is refused with a clear message."""
+    extra = dict(norm="layernorm", activation="gelu", tie_word_embeddings=True)
+    MODEL.update(extra)
+    try:
+        full_path = str(tmp_path / "full.pt")
+        ref = _reference(full_path, 4)
+        res = run_distributed(_worker_v, 2, full_path, dict(zero_stage=3, batch_size=2), 4, extra)
+        for r in res:
+            for a, b in zip(r, ref):
+                assert abs(a - b) < 2e-3, (r, ref)
+        with pytest.raises(RuntimeError, match="tie_word_embeddings"):
+            run_distributed(_worker_v, 2, full_path, dict(pipeline_parallel=2, batch_size=2, gradient_accumulation_steps=2), 4, extra)
+    finally:
+        for k in extra:
+            MODEL.pop(k, None)
