@@ -281,6 +281,8 @@ class MeasuredCostModel:
             for pp in (1, 2, 4, 8):
                 if tp * pp > n or n % (tp * pp) or pp > self.m.layers or pins.get("pipeline_parallel") not in (None, pp):
                     continue
+                if pp > 1 and getattr(self.m, "tie_word_embeddings", False):
+                    continue           # a tied embedding / head cannot straddle pipeline stages (models/gpt.py)
                 dp = n // (tp * pp)
                 for zero in (0, 1, 2, 3):
                     if pins.get("zero_stage") not in (None, zero):
