@@ -37,6 +37,14 @@ class ModelConfig:
             self.head_dim = self.hidden // self.heads
         if self.rope is None:
             self.rope = {"base": 10000, "scaling": None}
+        sc = self.rope.get("scaling")
+        if isinstance(sc, dict):
+            # HF-style {"type": "linear", "factor": 2.0} -> the reference's flat form ("scaling": "linear", "factor": 2.0);
+            # left as a dict it would compare unequal to every known mode and be ignored without a word
+            self.rope = {**self.rope, "scaling": sc.get("type") or sc.get("rope_type"),
+                         "factor": float(sc.get("factor", self.rope.get("factor", 1.0)))}
+        if self.rope.get("scaling") not in (None, "linear", "su"):
+            raise ValueError(f"unknown rope scaling {self.rope.get('scaling')!r} (None | 'linear' | 'su')")
 
     # ---- derived quantities -------------------------------------------------------------------
     @property
