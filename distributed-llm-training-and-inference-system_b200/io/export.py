@@ -172,6 +172,22 @@ def export_checkpoint(ckpt: str | Path, out: str | Path, fmt: str = "safetensors
             shutil.copy2(ckpt / f, out / f)
     for f in ckpt.glob("tokenizer*"):
         shutil.copy2(f, out / f.name)
+    if hf_names and (ckpt / "model_config.json").exists():
+        # config.json so that transformers' LlamaForCausalLM.from_pretrained(out) loads the artifact directly
+        mc = json.loads((ckpt / "model_config.json").read_text())
+        if mc.get("norm", "rmsnorm") != "rmsnorm" or mc.get("activation", "silu") != "silu":
+            raise ValueError("--hf-names writes the LlamaForCausalLM layout: the model must use RMSNorm and a SwiGLU MLP")
+        rope = mc.get("rope") or {}
+        hf_cfg = {"architectures": ["LlamaForCausalLM"], "model_type": "llama", "vocab_size": mc["vocab_size"],
+                  "hidden_size": mc["hidden"], "intermediate_size": mc["ffn"], "num_hidden_layers": mc["layers"],
+                  "num_attention_heads": mc["heads"], "num_key_value_heads": mc["heads"], "hidden_act": "silu",
+                  "max_position_embeddings": mc.get("max_position_embeddings", 4096),
+                  "rms_norm_eps": mc.get("layer_norm_eps", 1e-5), "rope_theta": float(rope.get("base", 10000)),
+                  "tie_word_embeddings": bool(mc.get("tie_word_embeddings", False)), "attention_bias": False,
+                  "torch_dtype": str(next(iter(full.values())).dtype).replace("torch.", "")}
+        if rope.get("scaling") == "linear" and float(rope.get("factor", 1.0)) != 1.0:
+            hf_cfg["rope_scaling"] = {"rope_type": "linear", "factor": float(rope["factor"])}
+        (out / "config.json").write_text(json.dumps(hf_cfg, indent=2))
     (out / "export.json").write_text(json.dumps({"format": fmt, "source": str(ckpt), "hf_names": hf_names,
                                                  "tensors": len(full)}, indent=2))
     return out

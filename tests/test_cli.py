@@ -225,3 +225,24 @@ def test_checkpoint_latest_resumes_from_this_runs_output_dir(tmp_path):
     text = (r.stdout + r.stderr).replace("\n", " ")
     assert "resumed from" in text and "at step 5" in text              # final/ (step 5) beats checkpoint-4
     assert json.loads((out / "final" / "training_state.json").read_text())["global_step"] == 7
+
+
+def test_hf_named_export_loads_in_transformers_with_identical_logits(tmp_path):
+    """`export convert --hf-names` writes a directory that LlamaForCausalLM.from_pretrained reads as is, and the two
+    implementations agree on the logits."""
+    transformers = pytest.importorskip("transformers")
+    import torch
+    out = tmp_path / "run"
+    assert run("train", "launch", "--model", "gpt-tiny", "--output-dir", str(out), "--batch-size", "2", "--seq-len", "32",
+               "--max-steps", "2", "--mixed-precision", "fp32", "--distributed-backend", "gloo", timeout=300).returncode == 0
+    art = tmp_path / "hf"
+    r = run("export", "convert", "--ckpt", str(out / "final"), "--out", str(art), "--format", "safetensors", "--hf-names")
+    assert r.returncode == 0 and (art / "config.json").exists(), r.stdout + r.stderr
+    hf = transformers.LlamaForCausalLM.from_pretrained(str(art), torch_dtype=torch.float32)
+    from llmctl_b200.serve.engine import load_model_for_inference
+    model, cfg, _, _ = load_model_for_inference(str(out / "final"), device="cpu")
+    ids = torch.randint(3, cfg.vocab_size, (1, 24))
+    with torch.no_grad():
+        a = hf(ids).logits[0].float()
+        b = model(ids).float()[:, :cfg.vocab_size]
+    assert float((a - b).abs().max()) < 1e-4
