@@ -144,6 +144,63 @@ def to_hf_llama(full: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
     return out
 
 
+
+def from_hf_llama(hf: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
+    """Inverse of ``to_hf_llama``: HF LlamaForCausalLM keys -> this framework's names (q|k|v and gate|up re-packed)."""
+    out: Dict[str, torch.Tensor] = {}
+    inv = [(r"^model\.embed_tokens\.weight$", "embed.weight"), (r"^model\.norm\.weight$", "final_norm.weight"),
+           (r"^lm_head\.weight$", "lm_head.weight"),
+           (r"^model\.layers\.(\d+)\.input_layernorm\.weight$", r"blocks.\1.norm1.weight"),
+           (r"^model\.layers\.(\d+)\.post_attention_layernorm\.weight$", r"blocks.\1.norm2.weight"),
+           (r"^model\.layers\.(\d+)\.self_attn\.o_proj\.weight$", r"blocks.\1.attn.out.weight"),
+           (r"^model\.layers\.(\d+)\.mlp\.down_proj\.weight$", r"blocks.\1.mlp.down.weight")]
+    layers = sorted({int(m.group(1)) for k in hf for m in [re.match(r"^model\.layers\.(\d+)\.", k)] if m})
+    for i in layers:
+        pre = f"model.layers.{i}."
+        try:
+            out[f"blocks.{i}.attn.qkv.weight"] = torch.cat([hf[pre + f"self_attn.{n}_proj.weight"] for n in ("q", "k", "v")], 0)
+            out[f"blocks.{i}.mlp.up.weight"] = torch.cat([hf[pre + "mlp.gate_proj.weight"], hf[pre + "mlp.up_proj.weight"]], 0)
+        except KeyError as e:
+            raise KeyError(f"HF checkpoint is missing {e.args[0]} (only LlamaForCausalLM-style layouts are supported)") from None
+        if hf[pre + "self_attn.k_proj.weight"].shape[0] != hf[pre + "self_attn.q_proj.weight"].shape[0]:
+            raise ValueError("grouped-query attention checkpoints (num_key_value_heads < num_attention_heads) are not supported")
+    for k, v in hf.items():
+        if re.search(r"\.(q|k|v)_proj\.weight$|\.(gate|up)_proj\.weight$|rotary_emb\.inv_freq$", k):
+            continue
+        for pat, rep in inv:
+            if re.match(pat, k):
+                out[re.sub(pat, rep, k)] = v
+                break
+        else:
+            if k.endswith(".bias"):
+                raise ValueError(f"HF checkpoint has a bias tensor ({k}); this model family has none")
+    return out
+
+
+def load_pretrained_state_dict(path: str | Path) -> Dict[str, torch.Tensor]:
+    """Full (unsharded) weights in this framework's names from a directory that holds either one of our checkpoints
+    / exports (single file or TP/PP shards + index) or an HF LLaMA checkpoint (``config.json`` + one
+    ``model.safetensors`` or ``model-0000x-of-0000y.safetensors`` shards with a ``weight_map`` index)."""
+    from safetensors.torch import load_file
+    path = Path(path)
+    idx = path / "model.safetensors.index.json"
+    if idx.exists() and "weight_map" in json.loads(idx.read_text()):
+        full: Dict[str, torch.Tensor] = {}
+        for fname in sorted(set(json.loads(idx.read_text())["weight_map"].values())):
+            full.update(load_file(str(path / fname)))
+    elif (path / "model.safetensors").exists() or idx.exists():
+        full = consolidate_to_state_dict(path)
+    else:
+        raise FileNotFoundError(f"no model.safetensors (or index) under {path}")
+    if any(k.startswith("model.layers.") or k.startswith("model.embed_tokens") for k in full):
+        full = from_hf_llama(full)
+    return full
+
+
+def has_weights(path: str | Path) -> bool:
+    p = Path(str(path))
+    return p.is_dir() and ((p / "model.safetensors").exists() or (p / "model.safetensors.index.json").exists())
+
 SUPPORTED_FORMATS = ("safetensors",)
 DECLARED_FORMATS = ("safetensors", "onnx", "tensorrt", "gguf")
 DECLARED_QUANT = ("int8-awq", "int4-gptq")

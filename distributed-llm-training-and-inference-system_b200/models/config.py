@@ -92,6 +92,37 @@ class ModelConfig:
             return cls.from_dict(json.load(f))
 
 
+def from_hf_config(hf: Dict[str, Any], name: str = "hf-model") -> ModelConfig:
+    """An HF ``config.json`` of the LLaMA family -> ModelConfig (the reference fine-tunes whatever
+    ``AutoModelForCausalLM.from_pretrained(model_name_or_path)`` returns, reference llmctl/runtime/engine.py:126-140;
+    here the architecture is ours, so only layouts we can represent exactly are accepted)."""
+    mt = hf.get("model_type", "")
+    if mt not in ("llama", "mistral"):
+        raise ValueError(f"HF model_type {mt!r} is not supported (llama-style decoder-only models only)")
+    heads, kv = int(hf["num_attention_heads"]), int(hf.get("num_key_value_heads") or hf["num_attention_heads"])
+    if kv != heads:
+        raise ValueError(f"grouped-query attention (num_key_value_heads={kv} < num_attention_heads={heads}) is not supported")
+    if hf.get("attention_bias") or hf.get("mlp_bias"):
+        raise ValueError("HF checkpoints with attention / MLP biases are not supported")
+    if hf.get("hidden_act", "silu") != "silu":
+        raise ValueError(f"hidden_act {hf.get('hidden_act')!r} is not supported (silu / SwiGLU only)")
+    if mt == "mistral" and hf.get("sliding_window"):
+        raise ValueError("sliding-window attention is not supported")
+    rope: Dict[str, Any] = {"base": float(hf.get("rope_theta", 10000.0)), "scaling": None}
+    rs = hf.get("rope_scaling")
+    if rs:
+        kind = rs.get("rope_type") or rs.get("type")
+        if kind not in (None, "default", "linear"):
+            raise ValueError(f"rope_scaling type {kind!r} is not supported (linear only)")
+        if kind == "linear":
+            rope.update(scaling="linear", factor=float(rs.get("factor", 1.0)))
+    return ModelConfig(name=name, layers=int(hf["num_hidden_layers"]), hidden=int(hf["hidden_size"]),
+                       ffn=int(hf["intermediate_size"]), heads=heads, head_dim=hf.get("head_dim"),
+                       vocab_size=int(hf["vocab_size"]), max_position_embeddings=int(hf.get("max_position_embeddings", 4096)),
+                       rope=rope, layer_norm_eps=float(hf.get("rms_norm_eps", 1e-5)),
+                       tie_word_embeddings=bool(hf.get("tie_word_embeddings", False)))
+
+
 _ROPE_SU = {"base": 10000, "scaling": "su"}
 _ROPE_LINEAR = {"base": 10000, "scaling": "linear"}
 
@@ -128,4 +159,8 @@ def resolve_model(spec: str | Path | Dict[str, Any] | ModelConfig) -> ModelConfi
         return ModelConfig.from_file(p)
     if p.exists() and p.is_dir() and (p / "model_config.json").exists():
         return ModelConfig.from_file(p / "model_config.json")
+    if p.exists() and p.is_dir() and (p / "config.json").exists():
+        return from_hf_config(json.loads((p / "config.json").read_text()), name=p.name)
+    if p.exists() and p.is_dir():
+        raise FileNotFoundError(f"{p} has neither model_config.json nor an HF config.json")
     return get_preset(str(spec))

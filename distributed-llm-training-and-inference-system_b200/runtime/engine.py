@@ -233,6 +233,19 @@ class TrainingEngine:
                 fused.init_tp_workspace(max_tokens=c.batch_size * c.seq_len, hidden=max(cfg.hidden, cfg.ffn // st.tp * 2))
             except Exception as e:  # noqa: BLE001 - symmetric memory unavailable: NCCL collectives
                 self.logger.warning("fused TP workspace unavailable (%s: %s); using NCCL collectives", type(e).__name__, e)
+        # fine-tuning: a directory that carries weights (one of our checkpoints / exports, or an HF LLaMA checkpoint)
+        # initialises the model from them — sharded for this rank's TP / PP position
+        from ..io import export as export_io
+        if not isinstance(c.model_name_or_path, ModelConfig) and export_io.has_weights(c.model_name_or_path):
+            full = export_io.load_pretrained_state_dict(c.model_name_or_path)
+            local = export_io.shard_state_dict_for(full, self.model)
+            with torch.no_grad():
+                for k, prm in self.model.named_parameters():
+                    prm.copy_(local[k].to(prm.device, prm.dtype))
+            del full, local
+            self.pretrained_from = str(c.model_name_or_path)
+            if self.is_main:
+                self.logger.info("initialised weights from %s", c.model_name_or_path)
         from ..serve.tokenizer import load_tokenizer
         self.tokenizer = load_tokenizer(c.model_name_or_path, cfg.vocab_size)
         if self.is_main:

@@ -44,11 +44,10 @@ def load_model_for_inference(artifact: str | Path, device: Optional[str] = None,
     dtype = dtype or (torch.bfloat16 if dev.type == "cuda" else torch.float32)
     p = Path(str(artifact))
     if p.is_dir():
-        mcfg = ModelConfig.from_file(p / "model_config.json")
+        from ..io.export import load_pretrained_state_dict
+        mcfg = resolve_model(p)                                  # model_config.json, or an HF config.json
         model = build_model(mcfg, dtype=dtype, device=dev)
-        full = consolidate_to_state_dict(p)
-        if any(k.startswith("model.layers.") for k in full):
-            raise ValueError("artifact uses HF tensor names; re-export without --hf-names to serve it here")
+        full = load_pretrained_state_dict(p)                     # our names or HF LlamaForCausalLM names
         local = shard_state_dict_for(full, model)
         with torch.no_grad():
             for k, prm in model.named_parameters():

@@ -246,3 +246,33 @@ def test_hf_named_export_loads_in_transformers_with_identical_logits(tmp_path):
         a = hf(ids).logits[0].float()
         b = model(ids).float()[:, :cfg.vocab_size]
     assert float((a - b).abs().max()) < 1e-4
+
+
+def test_finetune_and_serve_from_an_hf_llama_checkpoint(tmp_path):
+    """`--model <dir>` with an HF LLaMA checkpoint (config.json + sharded safetensors): same logits as transformers,
+    and a TP=2 fine-tuning run starts from those weights (the reference's main use: fine-tune an HF model)."""
+    transformers = pytest.importorskip("transformers")
+    import torch
+    torch.manual_seed(0)
+    hf = transformers.LlamaForCausalLM(transformers.LlamaConfig(
+        vocab_size=500, hidden_size=64, intermediate_size=176, num_hidden_layers=2, num_attention_heads=4,
+        num_key_value_heads=4, max_position_embeddings=128, rms_norm_eps=1e-6, tie_word_embeddings=False)).float()
+    src = tmp_path / "hf_src"
+    hf.save_pretrained(str(src), safe_serialization=True, max_shard_size="200KB")
+    assert (src / "model.safetensors.index.json").exists()
+    from llmctl_b200.serve.engine import load_model_for_inference
+    model, cfg, _, _ = load_model_for_inference(str(src), device="cpu")
+    ids = torch.randint(3, 500, (2, 20))
+    with torch.no_grad():
+        a = hf(ids).logits.float().reshape(-1, 500)
+        b = model(ids).float()[:, :500]
+    assert float((a - b).abs().max()) < 1e-4
+    r = run("train", "launch", "--model", str(src), "--output-dir", str(tmp_path / "ft"), "--batch-size", "2", "--seq-len", "32",
+            "--max-steps", "2", "--mixed-precision", "fp32", "--distributed-backend", "gloo", "--gpus-per-node", "2",
+            "--tensor-parallel", "2", timeout=300)
+    assert r.returncode == 0 and "initialised weights from" in (r.stdout + r.stderr).replace("\n", " "), r.stdout[-1500:]
+    gqa = json.loads((src / "config.json").read_text()); gqa["num_key_value_heads"] = 2
+    (src / "config.json").write_text(json.dumps(gqa))
+    r = run("train", "launch", "--model", str(src), "--output-dir", str(tmp_path / "ft2"), "--max-steps", "1",
+            "--mixed-precision", "fp32", "--distributed-backend", "gloo", timeout=300)
+    assert r.returncode != 0 and "grouped-query" in (r.stdout + r.stderr).replace("\n", " ")
