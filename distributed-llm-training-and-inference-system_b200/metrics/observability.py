@@ -166,6 +166,18 @@ class PrometheusExporter:
             self.sys_gpu_util.labels(gpu_id=str(i)).set(v)
 
 
+def _endpoint_reachable(endpoint: str, timeout: float = 0.5) -> bool:
+    import socket
+    from urllib.parse import urlparse
+    u = urlparse(endpoint)
+    host, port = u.hostname or "localhost", u.port or (443 if u.scheme == "https" else 80)
+    try:
+        with socket.create_connection((host, port), timeout=timeout):
+            return True
+    except OSError:
+        return False
+
+
 class OpenTelemetryExporter:
     """OTLP/HTTP spans (one per training step / inference request) and two histograms."""
 
@@ -176,6 +188,12 @@ class OpenTelemetryExporter:
         from opentelemetry.sdk.trace import TracerProvider
         from opentelemetry.sdk.trace.export import BatchSpanProcessor
         self.endpoint = endpoint.rstrip("/")
+        if not _endpoint_reachable(self.endpoint):
+            # presets ship the reference's default collector address; with nobody listening the exporters would print
+            # a connection traceback for every batch — say it once and keep the spans in-process instead
+            import warnings
+            warnings.warn(f"OTLP collector {self.endpoint} is not reachable: telemetry export disabled for this run")
+            raise ConnectionError(f"OTLP collector {self.endpoint} is not reachable")
         res = Resource.create({"service.name": service_name})
         self.provider = TracerProvider(resource=res)
         try:
