@@ -237,7 +237,6 @@ class InferenceEngine:
         self.max_context = min(self.cfg.max_position_embeddings, max_batch_tokens)
         self.stats = {"steps": 0, "prefill_tokens": 0, "decode_tokens": 0, "preemptions": 0, "prefill_time_s": 0.0,
                       "decode_time_s": 0.0, "decode_steps": 0}
-        self._scratch = None
         # decode runs as a replayed CUDA graph per (batch bucket, context bucket): the step is launch-bound
         # (~10 small kernels per layer), so replay removes the per-kernel Python + launch cost.  TP ranks keep the
         # eager path (the peer-signal epochs of the fused all-reduce are launch arguments, not graph-replayable).
@@ -391,7 +390,7 @@ class InferenceEngine:
         ctx = [len(s.all_ids) for s in seqs]               # context length including the token being processed
         max_ctx = max(ctx)
         if self.cuda_graphs:
-            Bb = self._bucket(B, 1, self.sched_max_batch())
+            Bb = self._bucket(B, 1, max(self.max_batch_size, 1))
             cb = self._bucket(max_ctx, 256, max(self.max_context, max_ctx))
         else:
             Bb, cb = B, max_ctx
@@ -421,9 +420,6 @@ class InferenceEngine:
         if g is None:
             g = self._graphs[key] = _DecodeGraph(self, inp, Bb, cb)
         return g.replay()[:B]
-
-    def sched_max_batch(self) -> int:
-        return max(int(getattr(self.sched, "max_batch_size", 8)), 1)
 
     def _gather_vocab(self, logits: torch.Tensor) -> torch.Tensor:
         """TP: logits are vocab shards; gather to the full vocabulary (tiny [B, V] all-gather)."""
