@@ -123,9 +123,11 @@ class SyntheticTimedLoader:
 
 def run(args) -> dict:
     ref = HERE / "_ref"
-    if not (ref / "llmctl" / "runtime" / "engine.py").exists():
-        return {"impl": "reference", "unavailable": "baseline/_ref is empty: run `python -m pip install --no-index "
-                "--no-build-isolation --no-deps --find-links /opt/wheelhouse --target baseline/_ref /root/reference`"}
+    sys.path.insert(0, str(HERE))
+    from provision import ensure_reference
+    ok, how = ensure_reference()
+    if not ok:
+        return {"impl": "reference", "unavailable": how[:300]}
     import transformers  # noqa: F401  (imported BEFORE the shim is visible, so HF never tries to use "accelerate")
     sys.path.insert(0, str(HERE / "shims"))
     sys.path.insert(0, str(ref))
