@@ -175,6 +175,7 @@ def run_native(args) -> dict:
     ev0.record()
     for i in range(K):
         loss = step_resident(W + i)
+    eng.optimizer.sync_params()       # the last step's parameter publication (side stream) belongs to the timed region
     ev1.record()
     barrier()
     launches = native.launch_count - launches0
@@ -199,6 +200,7 @@ def run_native(args) -> dict:
         for _ in range(K):
             out = eng.train_step()
             _ = float(out["loss"])          # device -> host read of the step result
+        eng.optimizer.sync_params()
         e1.record()
         barrier()
         wall_ms = (time.perf_counter() - t0) * 1e3

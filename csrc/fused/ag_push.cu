@@ -1,0 +1,100 @@
+// K1 producer side: sequence-parallel all-gather by PUSH.
+//
+// Every rank owns rows [r*Ms, (r+1)*Ms) of the activation X[M, K].  Instead of the consumer pulling seven remote
+// shards (NVLink read round trips in front of the tensor core), the owner pushes its rows into the same offset of
+// every rank's symmetric buffer Xg — one NVLS `multimem.st` per 16 bytes, replicated by the switch (egress = one
+// shard, not seven), or P2P stores when no multicast mapping exists — slab by slab, and raises the slab's epoch
+// flag on every rank once the slab is complete.  The consumer is the tcgen05 GEMM itself
+// (llmctl_gemm_bf16_gated, csrc/gemm/gemm_tcgen05.cu): all 148 SMs do MMAs, its TMA producer waits per tile for
+// the flags of the rows it needs, so the transfer of later slabs overlaps the math on earlier ones.
+//
+// Flag f = row / rows_per_flag lives at pads[dst][flag_base + f]; epochs increase per call, flags are never reset.
+// Buffer reuse: Xg alternates between two buffers; a rank can only push call n after its own GEMM n-1 finished,
+// which waited for every peer's push n-1, which those peers issued after their GEMM n-2 — so nobody still reads the
+// buffer that call n overwrites.
+//
+// Reference: none (SP is a preset flag only: reference configs/presets/llama-7b-a100x8.toml:36).  SURVEY.md §2.6.b K1.
+#include "../comm/symm.cuh"
+#include "../common/util.cuh"
+
+namespace llmctl {
+using namespace symm;
+
+constexpr int kPushThreads = 512;
+
+__global__ void __launch_bounds__(kPushThreads)
+ag_push_kernel(const uint4* __restrict__ src, uint4* __restrict__ mc_dst, PeerTable peers, long long dst_off_vec,
+               long long slab_vec, int n_slabs, PeerTable pads, int flag_base, int first_flag, int rank, int world,
+               uint32_t epoch, uint32_t* __restrict__ counters, int skip_self) {
+  __shared__ unsigned int s_last;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (int sl = 0; sl < n_slabs; ++sl) {
+    const uint4* s_src = src + sl * slab_vec;
+    const long long base = dst_off_vec + sl * slab_vec;
+    long long v = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+    if (mc_dst != nullptr) {
+      for (; v + stride < slab_vec; v += 2 * stride) {
+        const uint4 a = s_src[v], b = s_src[v + stride];
+        ptx::multimem_st_v4(mc_dst + base + v, a);
+        ptx::multimem_st_v4(mc_dst + base + v + stride, b);
+      }
+      for (; v < slab_vec; v += stride) ptx::multimem_st_v4(mc_dst + base + v, s_src[v]);
+    } else {
+      for (; v < slab_vec; v += stride) {
+        const uint4 a = s_src[v];
+#pragma unroll
+        for (int i = 0; i < kMaxRanks; ++i) {
+          if (i < world) {
+            const int dst = (rank + i) % world;       // staggered: no egress hot-spot
+            if (dst == rank && skip_self) continue;
+            ptx::st_v4(reinterpret_cast<uint4*>(peers.ptr[dst]) + base + v, a);
+          }
+        }
+      }
+    }
+    // slab complete on this CTA -> the last CTA to get here raises the slab's flag on every rank
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const unsigned int done = atomicAdd(&counters[sl], 1u) + 1u;
+      s_last = (done == gridDim.x) ? 1u : 0u;
+      if (s_last) atomicExch(&counters[sl], 0u);
+    }
+    __syncthreads();
+    if (s_last && threadIdx.x < world && static_cast<int>(threadIdx.x) != rank)
+      signal_set(reinterpret_cast<uint32_t*>(pads.ptr[threadIdx.x]) + flag_base + first_flag + sl, epoch);
+    __syncthreads();
+  }
+}
+
+}  // namespace llmctl
+
+using namespace llmctl;
+LLMCTL_SYMM_WATCHDOG_MODULE(ag_push)
+
+// Push this rank's [rows, cols] bf16 block (contiguous, `src`) to rows [rank*rows, (rank+1)*rows) of every rank's
+// symmetric [world*rows, cols] buffer.
+//   xg / mc_xg : per-rank base pointers / NVLS multicast address (or NULL) of the symmetric buffer
+//   rows_per_flag : slab size; must divide rows.  Flags used: pads[*][flag_base + rank*rows/rows_per_flag + slab]
+//   counters   : >= rows/rows_per_flag zero-initialised uint32 in local memory (left zero on exit)
+//   src_in_xg  : 1 when `src` already IS this rank's block of the local buffer (no local write needed on the P2P path)
+LLMCTL_API int llmctl_ag_push(const void* src, llmctl::symm::PeerTable xg, void* mc_xg, int rows, int cols,
+                              int rows_per_flag, llmctl::symm::PeerTable pads, int flag_base, int rank, int world,
+                              unsigned int epoch, unsigned int* counters, int src_in_xg, int max_ctas,
+                              void* stream) {
+  LLMCTL_BEGIN();
+  LLMCTL_REQUIRE(world >= 1 && world <= symm::kMaxRanks && cols % 8 == 0 && rows > 0 && rows_per_flag > 0 &&
+                 rows % rows_per_flag == 0 && rows / rows_per_flag <= 32 &&
+                 flag_base + world * (rows / rows_per_flag) <= 480);
+  const int n_slabs = rows / rows_per_flag;
+  const long long slab_vec = static_cast<long long>(rows_per_flag) * cols / 8;
+  const long long dst_off_vec = static_cast<long long>(rank) * rows * cols / 8;
+  long long grid = (slab_vec + kPushThreads - 1) / kPushThreads;
+  if (max_ctas <= 0) max_ctas = kNumSMs;
+  if (grid > max_ctas) grid = max_ctas;
+  if (grid < 1) grid = 1;
+  ag_push_kernel<<<static_cast<int>(grid), kPushThreads, 0, (cudaStream_t)stream>>>(
+      (const uint4*)src, (uint4*)mc_xg, xg, dst_off_vec, slab_vec, n_slabs, pads, flag_base, rank * n_slabs, rank,
+      world, epoch, counters, src_in_xg);
+  LLMCTL_RETURN_LAST();
+}

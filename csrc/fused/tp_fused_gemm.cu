@@ -1,14 +1,5 @@
-// K1 + K2: tensor/sequence-parallel GEMMs fused with their collective over NVLink peer memory.
-//
-// K1  ag_gemm   : sequence-parallel ALL-GATHER -> column-parallel GEMM in ONE kernel.
-//     Every rank owns rows [r*Ms, (r+1)*Ms) of the activation X[M,K] inside a symmetric buffer Xg (its norm
-//     kernel wrote them there).  CTAs [0, n_copy) are *copy* CTAs: they pull the peers' row blocks into the
-//     local Xg with TMA bulk copies (global(peer) -> smem ring -> global(local)), one peer chunk at a time in
-//     ring order (rank+1, rank+2, ...), and publish chunk_ready[c] when a chunk has landed.  The remaining
-//     CTAs run the tcgen05 GEMM (TMA operands, TMEM accumulators, UMMA 128x256x16): they walk the M chunks
-//     in the same ring order starting with the local one, and the TMA producer warp only waits for
-//     chunk_ready[c] of the chunk it is about to read.  The NVLink transfer of chunk i+1 therefore overlaps the
-//     MMAs of chunk i; the gathered Xg stays materialised for the wgrad GEMM of the backward pass.
+// K2: tensor/sequence-parallel row-parallel GEMM fused with its reduce-scatter over NVLink peer memory.
+// (K1, the all-gather -> GEMM direction, is csrc/fused/ag_push.cu + the gated GEMM in csrc/gemm/gemm_tcgen05.cu.)
 //
 // K2  gemm_rs   : row-parallel GEMM -> sequence-parallel REDUCE-SCATTER in ONE kernel.
 //     Partial sums D[M,N] = X[M,Kl] Wl^T are produced tile by tile; the epilogue converts each 128-row slab to
@@ -18,10 +9,12 @@
 //     been pushed, that destination's flag is raised.  The owner's follow-up kernel
 //     (llmctl_rs_reduce_rmsnorm, below) sums the `world` slots in fp32 in rank order — deterministic, no
 //     atomics — fused with the residual add and the RMSNorm that sits on the sequence shard (K3).
+//     The weight may be K-major ([N, Kl], forward) or MN-major ([Kl, N] = the forward weight of a column-parallel
+//     layer used untransposed for its dgrad).
 //
 // Reference: no TP/SP exists in the reference (planner integers only: reference
 // llmctl/cli/commands/plan.py:79-80,110-113; `sequence_parallel` flag: configs/presets/llama-7b-a100x8.toml:36).
-// Baseline to beat: NCCL all-gather + cuBLAS, cuBLAS + NCCL reduce-scatter, run back to back.
+// Baseline to beat: cuBLAS + NCCL reduce-scatter, run back to back.
 #include "../comm/symm.cuh"
 #include "../common/tma_host.h"
 #include "../common/util.cuh"
@@ -37,50 +30,30 @@ constexpr int kFBBytes = kFBN * kFBK * 2;
 constexpr int kFStageBytes = kFABytes + kFBBytes;
 constexpr int kFSmem = kFStages * kFStageBytes + 1024;
 constexpr int kFThreads = 192;
-constexpr int kCopyPiece = 16384;            // bytes per TMA bulk copy
-constexpr int kCopySlots = 12;               // smem ring of the copy CTAs (12 x 16 KB)
-constexpr int kCopyAhead = 8;                // loads in flight; the 4 spare slots decouple a load from the store
-                                             // that last used its slot (no wait on the store just issued)
-constexpr int kCopyStages = 4;               // store groups allowed in flight when a chunk is published
 constexpr int kEpiRowBytes = 128 + 16;       // K2 epilogue staging: 64 bf16 per row + pad (conflict-free 16 B access)
 constexpr int kEpiWarpBytes = 32 * kEpiRowBytes;
 constexpr int kFSmemRS = kFSmem + 4 * kEpiWarpBytes;
-
-__device__ __forceinline__ void bulk_store_1d(void* gdst, const void* smem_src, uint32_t bytes) {
-  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(
-                   reinterpret_cast<uint64_t>(gdst)),
-               "r"(smem_u32(smem_src)), "r"(bytes)
-               : "memory");
-}
-__device__ __forceinline__ void st_release_gpu(uint32_t* p, uint32_t v) {
-  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
 
 struct FusedArgs {
   int M, N, K;
   int rank, world;
   int rows_per_rank;          // Ms = M / world
   uint32_t epoch;
-  int n_copy;                 // K1: number of copy CTAs (0 for K2)
 };
 
 // --------------------------------------------------------------------------------------------------
-// Shared GEMM core (1-CTA, 128 x 256 tile).  kMode 1 = K1 (wait for chunk_ready before loading A),
-// kMode 2 = K2 (epilogue pushes bf16 tiles to the owner's staging slot).
-// Tiles are enumerated chunk-major: chunk i covers M rows of rank c_i = (rank + i [+1 for K2]) % world.
+// GEMM core (1-CTA, 128 x 256 tile) whose epilogue pushes bf16 tiles to the owner's staging slot.
+// Tiles are enumerated chunk-major: chunk i covers the M rows owned by rank c_i = (rank + i + 1) % world.
 // --------------------------------------------------------------------------------------------------
-template <int kMode>
+template <bool B_MN>
 __global__ void __launch_bounds__(kFThreads, 1)
-tp_fused_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                     __nv_bfloat16* __restrict__ C, long long ldc, FusedArgs a,
-                     PeerTable xg,                 // K1: symmetric Xg (per-rank base);  K2: staging buffers
-                     PeerTable pads, uint32_t* __restrict__ local_flags /* chunk_ready / counters */) {
+gemm_rs_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, FusedArgs a,
+               PeerTable xg /* staging buffers */, PeerTable pads, uint32_t* __restrict__ local_flags /* counters */) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t bar_full[kFStages];
   __shared__ uint64_t bar_empty[kFStages];
   __shared__ uint64_t bar_tfull[2];
   __shared__ uint64_t bar_tempty[2];
-  __shared__ uint64_t bar_copy[kCopySlots];
   __shared__ uint32_t tmem_base_smem;
 
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -89,93 +62,9 @@ tp_fused_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
   const int lane = threadIdx.x & 31;
   const int Ms = a.rows_per_rank;
 
-  // ================================ K1 copy CTAs ================================
-  if (kMode == 1 && static_cast<int>(blockIdx.x) < a.n_copy) {
-    if (threadIdx.x == 0) {
-      for (int i = 0; i < kCopySlots; ++i) mbar_init(&bar_copy[i], 1);
-      fence_mbar_init();
-      // announce that this rank's own rows are in place (written by the previous kernel on this stream)
-      if (blockIdx.x == 0)
-        for (int p = 0; p < a.world; ++p)
-          signal_set(reinterpret_cast<uint32_t*>(pads.ptr[p]) + a.rank, a.epoch);
-      const long long chunk_bytes = static_cast<long long>(Ms) * a.K * 2;
-      const int pieces = static_cast<int>((chunk_bytes + kCopyPiece - 1) / kCopyPiece);
-      // This CTA's work list, chunk-major in ring order: item w -> (chunk i = 1 + w / per_cta, piece).  Loads are
-      // issued kCopyStages ahead of the stores and the pipeline is never drained between chunks; a chunk is
-      // published once all of this CTA's stores for it are known complete (cp.async.bulk.wait_group) — the last of
-      // the n_copy CTAs to get there raises chunk_ready.
-      const int per_cta = (pieces - static_cast<int>(blockIdx.x) + a.n_copy - 1) / a.n_copy;   // my pieces per chunk
-      const int total = per_cta * (a.world - 1);
-      uint32_t phase_bits = 0;
-      int issued = 0, stored = 0, published = 0;      // work-item counters; `published` counts whole chunks
-      int waited_chunk = 0;                            // peers whose "rows ready" flag has been observed (1-based ring index)
-      auto item = [&](int w, int& src, long long& off, uint32_t& bytes) {
-        const int ci = 1 + w / per_cta;
-        src = (a.rank + ci) % a.world;
-        const int piece = static_cast<int>(blockIdx.x) + (w % per_cta) * a.n_copy;
-        off = static_cast<long long>(piece) * kCopyPiece;
-        bytes = static_cast<uint32_t>(min(static_cast<long long>(kCopyPiece), chunk_bytes - off));
-      };
-      auto publish_upto = [&](int n_chunks_done) {
-        while (published < n_chunks_done) {
-          const int src = (a.rank + 1 + published) % a.world;
-          __threadfence();
-          const uint32_t done = atomicAdd(&local_flags[16 + src], 1u) + 1u;
-          if (done == static_cast<uint32_t>(a.n_copy)) {
-            atomicExch(&local_flags[16 + src], 0u);
-            st_release_gpu(&local_flags[src], a.epoch);
-          }
-          ++published;
-        }
-      };
-      if (per_cta == 0) {
-        publish_upto(a.world - 1);                     // nothing to copy: still take part in the chunk counters
-      } else {
-        while (stored < total) {
-          while (issued < total && issued - stored < kCopyAhead) {
-            int src; long long off; uint32_t bytes;
-            item(issued, src, off, bytes);
-            const int ci = 1 + issued / per_cta;
-            if (ci > waited_chunk) {                   // first touch of this peer: its rows must be in place
-              signal_wait_ge(reinterpret_cast<const uint32_t*>(pads.ptr[a.rank]) + src, a.epoch);
-              waited_chunk = ci;
-            }
-            const int slot = issued % kCopySlots;
-            // the store that last used this slot is at least (kCopySlots - kCopyAhead) groups old: only it (and
-            // older ones) must have finished READING shared memory
-            tma_store_wait_read<kCopySlots - kCopyAhead>();
-            mbar_expect_tx(&bar_copy[slot], bytes);
-            bulk_load_1d(smem + slot * kCopyPiece,
-                         reinterpret_cast<const uint8_t*>(xg.ptr[src]) + static_cast<long long>(src) * chunk_bytes + off,
-                         bytes, &bar_copy[slot]);
-            ++issued;
-          }
-          int src; long long off; uint32_t bytes;
-          item(stored, src, off, bytes);
-          const int slot = stored % kCopySlots;
-          mbar_wait(&bar_copy[slot], (phase_bits >> slot) & 1u);
-          phase_bits ^= (1u << slot);
-          bulk_store_1d(reinterpret_cast<uint8_t*>(xg.ptr[a.rank]) + static_cast<long long>(src) * chunk_bytes + off,
-                        smem + slot * kCopyPiece, bytes);
-          tma_store_commit();
-          ++stored;
-          // chunks whose last store is older than the kCopyStages most recent groups are complete after this wait
-          const int safe_items = stored - kCopyStages;
-          if (safe_items > 0 && safe_items / per_cta > published) {
-            tma_store_wait<kCopyStages>();
-            publish_upto(safe_items / per_cta);
-          }
-        }
-        tma_store_wait<0>();
-        publish_upto(a.world - 1);
-      }
-    }
-    return;
-  }
-
   // ================================ GEMM CTAs ================================
-  const int cta = (kMode == 1) ? static_cast<int>(blockIdx.x) - a.n_copy : static_cast<int>(blockIdx.x);
-  const int n_cta = (kMode == 1) ? static_cast<int>(gridDim.x) - a.n_copy : static_cast<int>(gridDim.x);
+  const int cta = static_cast<int>(blockIdx.x);
+  const int n_cta = static_cast<int>(gridDim.x);
   const int m_per_chunk = (Ms + kFBM - 1) / kFBM;
   const int num_n = (a.N + kFBN - 1) / kFBN;
   const int tiles_per_chunk = m_per_chunk * num_n;
@@ -207,7 +96,7 @@ tp_fused_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
   auto decode = [&](int tile, int& crank, int& m0, int& n0, int& m_end) {
     const int ci = tile / tiles_per_chunk;
     const int t = tile % tiles_per_chunk;
-    crank = (a.rank + ci + (kMode == 2 ? 1 : 0)) % a.world;
+    crank = (a.rank + ci + 1) % a.world;
     m0 = crank * Ms + (t % m_per_chunk) * kFBM;
     n0 = (t / m_per_chunk) * kFBN;
     m_end = (crank + 1) * Ms;
@@ -217,22 +106,22 @@ tp_fused_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      int ready_chunk = -1;
       for (int tile = cta; tile < num_tiles; tile += n_cta) {
         int crank, m0, n0, m_end;
         decode(tile, crank, m0, n0, m_end);
-        if (kMode == 1 && crank != a.rank && crank != ready_chunk) {
-          while (static_cast<int32_t>(ld_acquire_gpu(&local_flags[crank]) - a.epoch) < 0) __nanosleep(64);
-          fence_proxy_async_all();      // generic-proxy flag read -> async-proxy (TMA) data reads
-          ready_chunk = crank;
-        }
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&bar_empty[stage], phase ^ 1u);
           uint8_t* sA = smem + stage * kFStageBytes;
           uint8_t* sB = sA + kFABytes;
           mbar_expect_tx(&bar_full[stage], kFStageBytes);
           tma_load_2d(sA, &tmA, &bar_full[stage], kb * kFBK, m0);
-          tma_load_2d(sB, &tmB, &bar_full[stage], kb * kFBK, n0);
+          if (!B_MN) {
+            tma_load_2d(sB, &tmB, &bar_full[stage], kb * kFBK, n0);
+          } else {
+#pragma unroll
+            for (int g = 0; g < kFBN / 64; ++g)
+              tma_load_2d(sB + g * 8192, &tmB, &bar_full[stage], n0 + g * 64, kb * kFBK);
+          }
           if (++stage == kFStages) {
             stage = 0;
             phase ^= 1u;
@@ -242,7 +131,7 @@ tp_fused_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     }
   } else if (warp == 1) {
     if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(kFBM, kFBN, 0u, 0u);
+      constexpr uint32_t idesc = make_idesc_bf16(kFBM, kFBN, 0u, B_MN ? 1u : 0u);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
@@ -259,7 +148,9 @@ tp_fused_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
 #pragma unroll
           for (int k = 0; k < kFBK / 16; ++k)
             umma_ss<1>(d_tmem, make_smem_desc(a_addr + k * 32, 16, 1024, 2),
-                       make_smem_desc(b_addr + k * 32, 16, 1024, 2), idesc, (kb | k) != 0 ? 1u : 0u);
+                       B_MN ? make_smem_desc(b_addr + k * 2048, 8192, 1024, 2)
+                            : make_smem_desc(b_addr + k * 32, 16, 1024, 2),
+                       idesc, (kb | k) != 0 ? 1u : 0u);
           umma_commit<1>(&bar_empty[stage]);
           if (++stage == kFStages) {
             stage = 0;
@@ -280,19 +171,8 @@ tp_fused_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
       decode(tile, crank, m0, n0, m_end);
       mbar_wait(&bar_tfull[acc], aphase);
       tc_fence_after();
-      const int row = m0 + q * 32 + lane;
-      const bool row_ok = row < m_end && row < a.M;
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(acc * kFBN);
-      __nv_bfloat16* crow;
-      if (kMode == 2) {
-        // owner's staging slot for this source rank: stage[rank][Ms, N]; row index local to the owner
-        __nv_bfloat16* base = reinterpret_cast<__nv_bfloat16*>(xg.ptr[crank]) +
-                              static_cast<long long>(a.rank) * Ms * a.N;
-        crow = base + static_cast<long long>(row - crank * Ms) * a.N + n0;
-      } else {
-        crow = C + static_cast<long long>(row) * ldc + n0;
-      }
-      if (kMode == 2) {
+      {
         // Remote stores must be wide: stage 64 columns of the warp's 32 rows in shared memory (row = lane), then
         // let 8 consecutive lanes write one row's 128 contiguous bytes -> full-size NVLink write packets.
         uint8_t* st = smem + kFStages * kFStageBytes + q * kEpiWarpBytes;
@@ -328,31 +208,13 @@ tp_fused_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
           }
           __syncwarp();
         }
-      } else {
-#pragma unroll 1
-      for (int c = 0; c < kFBN / 32; ++c) {
-        uint32_t r[32];
-        tmem_ld_x32(t_row + c * 32, r);
-        tmem_ld_wait();
-        if (row_ok) {
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const int col = n0 + c * 32 + j * 8;
-            if (col < a.N) {
-              float f[8];
-#pragma unroll
-              for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(r[j * 8 + e]);
-              store8(crow + c * 32 + j * 8, pack8(f));
-            }
-          }
-        }
-      }
       }
       tc_fence_before();
-      __syncwarp();
-      if (kMode == 2) {
-        // count finished (tile, warp) pairs per destination; the last one raises the destination's flag
+      {
+        // count finished (tile, warp) pairs per destination; the last one raises the destination's flag.
+        // Order: every lane's remote stores -> system fence -> warp converges -> lane 0 publishes.
         __threadfence_system();
+        __syncwarp();
         if (lane == 0) {
           const uint32_t done = atomicAdd(&local_flags[crank], 1u) + 1u;
           if (done == static_cast<uint32_t>(tiles_per_chunk * 4)) {
@@ -454,38 +316,12 @@ static int fused_num_sms() {
 using namespace llmctl;
 LLMCTL_SYMM_WATCHDOG_MODULE(tp_fused_gemm)
 
-// K1.  xg: symmetric activation buffer [M, K] bf16 on every rank (rank r's rows [r*Ms,(r+1)*Ms) valid on entry,
-// all rows valid locally on exit).  W: [N, K] local weight shard.  C: [M, N] local output.
-// local_flags: 32 zero-initialised uint32 in local device memory (reused across calls).
-// pads slots [0, world) are used.  epoch must increase by 1 per call on every rank.
-LLMCTL_API int llmctl_ag_gemm(llmctl::symm::PeerTable xg, const void* W, void* C, int M, int N, int K,
-                              long long ldw, long long ldc, llmctl::symm::PeerTable pads,
-                              unsigned int* local_flags, int rank, int world, unsigned int epoch,
-                              int n_copy, void* stream) {
-  LLMCTL_BEGIN();
-  LLMCTL_REQUIRE(world >= 1 && world <= symm::kMaxRanks && M % world == 0 && K % 8 == 0 && N % 8 == 0);
-  LLMCTL_REQUIRE((static_cast<long long>(M / world) * K * 2) % 16 == 0);
-  CUtensorMap tmA, tmB;
-  int rc = get_tmap_2d_bf16(&tmA, xg.ptr[rank], M, K, K, kFBM, kFBK, 1);
-  if (rc) LLMCTL_FAIL(rc, "tensor map A");
-  rc = get_tmap_2d_bf16(&tmB, W, N, K, ldw, kFBN, kFBK, 1);
-  if (rc) LLMCTL_FAIL(rc, "tensor map B");
-  auto kern = tp_fused_gemm_kernel<1>;
-  LLMCTL_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kFSmem));
-  if (world == 1) n_copy = 0;
-  else if (n_copy <= 0) n_copy = (world > 2) ? 28 : 16;
-  FusedArgs a{M, N, K, rank, world, M / world, epoch, n_copy};
-  const int grid = fused_num_sms();
-  kern<<<grid, kFThreads, kFSmem, (cudaStream_t)stream>>>(tmA, tmB, (__nv_bfloat16*)C, ldc, a, xg, pads,
-                                                          local_flags);
-  LLMCTL_RETURN_LAST();
-}
-
-// K2.  X: [M, K] local activation (K = local shard of the contraction dim), W: [N, K] local weight shard.
+// K2.  X: [M, K] local activation (K = local shard of the contraction dim).  W: local weight shard, [N, K] (ldw = row
+// stride) or, with w_mn = 1, stored [K, N] (MN-major: a column-parallel forward weight reused for its dgrad).
 // stage: symmetric staging buffer [world, Ms, N] bf16 on every rank (slot s receives rank s's partial rows).
 // pads slots [8, 8 + world) are used.  local_flags: 32 zero-initialised uint32 (tile counters).
 LLMCTL_API int llmctl_gemm_rs(const void* X, const void* W, llmctl::symm::PeerTable stage, int M, int N, int K,
-                              long long ldx, long long ldw, llmctl::symm::PeerTable pads,
+                              long long ldx, long long ldw, int w_mn, llmctl::symm::PeerTable pads,
                               unsigned int* local_flags, int rank, int world, unsigned int epoch,
                               void* stream) {
   LLMCTL_BEGIN();
@@ -493,16 +329,23 @@ LLMCTL_API int llmctl_gemm_rs(const void* X, const void* W, llmctl::symm::PeerTa
   CUtensorMap tmA, tmB;
   int rc = get_tmap_2d_bf16(&tmA, X, M, K, ldx, kFBM, kFBK, 1);
   if (rc) LLMCTL_FAIL(rc, "tensor map A");
-  rc = get_tmap_2d_bf16(&tmB, W, N, K, ldw, kFBN, kFBK, 1);
+  if (!w_mn) rc = get_tmap_2d_bf16(&tmB, W, N, K, ldw, kFBN, kFBK, 1);
+  else rc = get_tmap_2d_bf16(&tmB, W, K, N, ldw, kFBK, 64, 1);
   if (rc) LLMCTL_FAIL(rc, "tensor map B");
-  auto kern = tp_fused_gemm_kernel<2>;
-  LLMCTL_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kFSmemRS));
-  FusedArgs a{M, N, K, rank, world, M / world, epoch, 0};
+  FusedArgs a{M, N, K, rank, world, M / world, epoch};
   const int Ms = M / world;
   const int tiles = ((Ms + kFBM - 1) / kFBM) * ((N + kFBN - 1) / kFBN) * world;
   int grid = fused_num_sms();
   if (tiles < grid) grid = tiles;
-  kern<<<grid, kFThreads, kFSmemRS, (cudaStream_t)stream>>>(tmA, tmB, nullptr, 0, a, stage, pads, local_flags);
+  if (w_mn) {
+    auto kern = gemm_rs_kernel<true>;
+    LLMCTL_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kFSmemRS));
+    kern<<<grid, kFThreads, kFSmemRS, (cudaStream_t)stream>>>(tmA, tmB, a, stage, pads, local_flags);
+  } else {
+    auto kern = gemm_rs_kernel<false>;
+    LLMCTL_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kFSmemRS));
+    kern<<<grid, kFThreads, kFSmemRS, (cudaStream_t)stream>>>(tmA, tmB, a, stage, pads, local_flags);
+  }
   LLMCTL_RETURN_LAST();
 }
 

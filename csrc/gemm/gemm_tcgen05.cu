@@ -17,12 +17,44 @@
 // `self.model(**batch)` (reference llmctl/runtime/engine.py:284) and `torch.matmul`
 // (reference llmctl/cli/commands/hw.py:317-337, llmctl/plugins/autotuning.py:89-114).
 // Baseline to beat: cuBLASLt bf16 (MEASURED_PEAKS.json).
-#include "../common/ptx.cuh"
+#include "../comm/symm.cuh"
 #include "../common/tma_host.h"
 #include "../common/util.cuh"
 
 namespace llmctl {
 using namespace ptx;
+
+// K1 (sequence-parallel all-gather -> GEMM) runs on this kernel: the rows of A live in a symmetric buffer that the
+// peers' producers fill over NVLink (csrc/fused/ag_push.cu); every `rows_per_flag` rows carry an epoch flag in the
+// local signal pad.  The TMA producer waits for the flags of the rows a tile needs, so the MMAs of what has arrived
+// overlap the transfer of what has not; tile rows are visited in arrival order (own chunk first, then the first
+// slab of every peer, the second slab of every peer, ...).  flags == NULL: plain GEMM.
+struct GemmGate {
+  const uint32_t* flags;
+  uint32_t epoch;
+  int rows_per_flag;
+  int own_lo, own_hi;        // rows that are local and never waited for
+  int perm;                  // 1: arrival-order permutation of the tile-row blocks
+  int rank, world;
+  int bpc, bps;              // tile-row blocks per rank chunk / per flag slab
+};
+__device__ __forceinline__ int gate_perm(const GemmGate& g, int i) {
+  if (!g.perm) return i;
+  if (i < g.bpc) return g.rank * g.bpc + i;
+  const int j = i - g.bpc, per_s = (g.world - 1) * g.bps;
+  const int s = j / per_s, w = j - s * per_s, p = w / g.bps, b = w - p * g.bps;
+  return ((g.rank + 1 + p) % g.world) * g.bpc + s * g.bps + b;
+}
+__device__ __forceinline__ void gate_wait(const GemmGate& g, int m0, int m_end) {
+  if (g.flags == nullptr) return;
+  const int R = g.rows_per_flag;
+  for (int f = m0 / R; f <= (m_end - 1) / R; ++f) {
+    const int fr = f * R;
+    if (fr >= g.own_lo && fr < g.own_hi) continue;
+    symm::signal_wait_ge(g.flags + f, g.epoch);
+  }
+  fence_proxy_async_all();      // generic-proxy flag reads -> async-proxy (TMA) reads of the rows
+}
 
 constexpr int kBM = 128;
 constexpr int kBK = 64;  // 64 bf16 = one 128-byte swizzle row
@@ -58,7 +90,7 @@ __device__ __forceinline__ void tile_to_mn(int tile, int num_m, int num_n, int& 
 template <int BN, bool A_MN, bool B_MN, typename OutT>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                    OutT* __restrict__ C, long long ldc, int M, int N, int K, int beta) {
+                    OutT* __restrict__ C, long long ldc, int M, int N, int K, int beta, const GemmGate gate) {
   using Cfg = GemmCfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t bar_full[Cfg::kStages];
@@ -106,8 +138,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         int mb_, nb_;
         tile_to_mn(tile, num_m, num_n, mb_, nb_);
+        mb_ = gate_perm(gate, mb_);
         const int m0 = mb_ * kBM;
         const int n0 = nb_ * BN;
+        gate_wait(gate, m0, min(m0 + kBM, M));
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&bar_empty[stage], phase ^ 1u);
           uint8_t* sA = smem + stage * Cfg::kStageBytes;
@@ -179,6 +213,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       int mb_, nb_;
       tile_to_mn(tile, num_m, num_n, mb_, nb_);
+      mb_ = gate_perm(gate, mb_);
       const int m0 = mb_ * kBM;
       const int n0 = nb_ * BN;
       mbar_wait(&bar_tfull[acc], aphase);
@@ -270,7 +305,7 @@ struct Gemm2Cfg {
 template <bool A_MN, bool B_MN, typename OutT>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
 gemm2_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                     OutT* __restrict__ C, long long ldc, int M, int N, int K, int beta) {
+                     OutT* __restrict__ C, long long ldc, int M, int N, int K, int beta, const GemmGate gate) {
   using Cfg = Gemm2Cfg;
   constexpr int BN = Cfg::kBN;
   extern __shared__ uint8_t smem_raw[];
@@ -323,8 +358,10 @@ gemm2_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
       for (int tile = pair; tile < num_tiles; tile += num_pairs) {
         int mb_, nb_;
         tile_to_mn(tile, num_m, num_n, mb_, nb_);
+        mb_ = gate_perm(gate, mb_);
         const int m0 = mb_ * (2 * kBM) + static_cast<int>(cta_rank) * kBM;
         const int n0 = nb_ * BN + static_cast<int>(cta_rank) * (BN / 2);
+        if (m0 < M) gate_wait(gate, m0, min(m0 + kBM, M));
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&bar_empty[stage], phase ^ 1u);
           uint8_t* sA = smem + stage * Cfg::kStageBytes;
@@ -398,6 +435,7 @@ gemm2_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     for (int tile = pair; tile < num_tiles; tile += num_pairs) {
       int mb_, nb_;
       tile_to_mn(tile, num_m, num_n, mb_, nb_);
+      mb_ = gate_perm(gate, mb_);
       const int m0 = mb_ * (2 * kBM) + static_cast<int>(cta_rank) * kBM;
       const int n0 = nb_ * BN;
       mbar_wait(&bar_tfull[acc], aphase);
@@ -479,7 +517,12 @@ static int num_sms() {
 
 template <int BN, bool A_MN, bool B_MN, typename OutT>
 static int launch_gemm(const void* A, const void* B, void* C, int M, int N, int K, long long lda,
-                       long long ldb, long long ldc, int beta, int max_ctas, cudaStream_t s) {
+                       long long ldb, long long ldc, int beta, int max_ctas, cudaStream_t s, GemmGate gate) {
+  if (gate.flags) {   // tile-row permutation needs whole tile blocks per chunk and per slab
+    gate.bpc = (M / gate.world) / kBM;
+    gate.bps = gate.rows_per_flag / kBM;
+    gate.perm = (gate.perm && (M / gate.world) % kBM == 0 && gate.rows_per_flag % kBM == 0 && M % gate.world == 0) ? 1 : 0;
+  }
   using Cfg = GemmCfg<BN>;
   CUtensorMap tmA, tmB;
   int rc;
@@ -496,24 +539,30 @@ static int launch_gemm(const void* A, const void* B, void* C, int M, int N, int 
   int grid = num_sms();
   if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
   if (tiles < grid) grid = tiles;
-  kern<<<grid, kGemmThreads, Cfg::kSmemBytes, s>>>(tmA, tmB, (OutT*)C, ldc, M, N, K, beta);
+  kern<<<grid, kGemmThreads, Cfg::kSmemBytes, s>>>(tmA, tmB, (OutT*)C, ldc, M, N, K, beta, gate);
   LLMCTL_RETURN_LAST();
 }
 
 template <int BN, typename OutT>
 static int dispatch_layout(int a_mn, int b_mn, const void* A, const void* B, void* C, int M, int N,
                            int K, long long lda, long long ldb, long long ldc, int beta,
-                           int max_ctas, cudaStream_t s) {
-  if (!a_mn && !b_mn) return launch_gemm<BN, false, false, OutT>(A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s);
-  if (!a_mn && b_mn) return launch_gemm<BN, false, true, OutT>(A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s);
-  if (a_mn && !b_mn) return launch_gemm<BN, true, false, OutT>(A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s);
-  return launch_gemm<BN, true, true, OutT>(A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s);
+                           int max_ctas, cudaStream_t s, const GemmGate& g) {
+  if (!a_mn && !b_mn) return launch_gemm<BN, false, false, OutT>(A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s, g);
+  if (!a_mn && b_mn) return launch_gemm<BN, false, true, OutT>(A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s, g);
+  if (a_mn && !b_mn) return launch_gemm<BN, true, false, OutT>(A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s, g);
+  return launch_gemm<BN, true, true, OutT>(A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s, g);
 }
 
 
 template <bool A_MN, bool B_MN, typename OutT>
 static int launch_gemm2(const void* A, const void* B, void* C, int M, int N, int K, long long lda,
-                        long long ldb, long long ldc, int beta, int max_ctas, cudaStream_t s) {
+                        long long ldb, long long ldc, int beta, int max_ctas, cudaStream_t s, GemmGate gate) {
+  if (gate.flags) {
+    gate.bpc = (M / gate.world) / (2 * kBM);
+    gate.bps = gate.rows_per_flag / (2 * kBM);
+    gate.perm = (gate.perm && (M / gate.world) % (2 * kBM) == 0 && gate.rows_per_flag % (2 * kBM) == 0 &&
+                 M % gate.world == 0) ? 1 : 0;
+  }
   using Cfg = Gemm2Cfg;
   CUtensorMap tmA, tmB;
   int rc;
@@ -531,18 +580,18 @@ static int launch_gemm2(const void* A, const void* B, void* C, int M, int N, int
   if (max_ctas > 0 && max_ctas / 2 < pairs) pairs = max_ctas / 2;
   if (pairs < 1) pairs = 1;
   if (tiles < pairs) pairs = tiles;
-  kern<<<2 * pairs, kGemmThreads, Cfg::kSmemBytes, s>>>(tmA, tmB, (OutT*)C, ldc, M, N, K, beta);
+  kern<<<2 * pairs, kGemmThreads, Cfg::kSmemBytes, s>>>(tmA, tmB, (OutT*)C, ldc, M, N, K, beta, gate);
   LLMCTL_RETURN_LAST();
 }
 
 template <typename OutT>
 static int dispatch_layout2(int a_mn, int b_mn, const void* A, const void* B, void* C, int M, int N,
                             int K, long long lda, long long ldb, long long ldc, int beta,
-                            int max_ctas, cudaStream_t s) {
-  if (!a_mn && !b_mn) return launch_gemm2<false, false, OutT>(A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s);
-  if (!a_mn && b_mn) return launch_gemm2<false, true, OutT>(A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s);
-  if (a_mn && !b_mn) return launch_gemm2<true, false, OutT>(A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s);
-  return launch_gemm2<true, true, OutT>(A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s);
+                            int max_ctas, cudaStream_t s, const GemmGate& g) {
+  if (!a_mn && !b_mn) return launch_gemm2<false, false, OutT>(A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s, g);
+  if (!a_mn && b_mn) return launch_gemm2<false, true, OutT>(A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s, g);
+  if (a_mn && !b_mn) return launch_gemm2<true, false, OutT>(A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s, g);
+  return launch_gemm2<true, true, OutT>(A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s, g);
 }
 
 }  // namespace llmctl
@@ -552,9 +601,9 @@ using namespace llmctl;
 // D[M,N] = op(A) op(B) (+ D if beta).  a_mn / b_mn select the operand storage (see file header).
 // out_fp32: D is fp32 (else bf16).  tile_n: 0 = auto, 128 or 256 (1-CTA tiles), 2 = 256x256 CTA-pair tile.  max_ctas: 0 = all SMs
 // (a smaller value leaves SMs free for a concurrent communication kernel).
-LLMCTL_API int llmctl_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K,
-                                long long lda, long long ldb, long long ldc, int a_mn, int b_mn,
-                                int out_fp32, int beta, int tile_n, int max_ctas, void* stream) {
+static int gemm_bf16_impl(const void* A, const void* B, void* C, int M, int N, int K,
+                          long long lda, long long ldb, long long ldc, int a_mn, int b_mn,
+                          int out_fp32, int beta, int tile_n, int max_ctas, void* stream, const GemmGate& g) {
   LLMCTL_BEGIN();
   LLMCTL_REQUIRE(M > 0 && N > 0 && K > 0);
   LLMCTL_REQUIRE(lda % 8 == 0 && ldb % 8 == 0 && N % 8 == 0);
@@ -566,8 +615,8 @@ LLMCTL_API int llmctl_gemm_bf16(const void* A, const void* B, void* C, int M, in
   // (measured on B200: 1.44-1.61 PFLOP/s vs 1.24-1.45 for the single-CTA 128x256 tile on the GPT-7B shapes)
   if (tile_n == 0 && M > 128 && N > 128) tile_n = 2;
   if (tile_n == 2) {   // 2-CTA pair tile 256 x 256 (cta_group::2)
-    if (out_fp32) return dispatch_layout2<float>(a_mn, b_mn, A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s);
-    return dispatch_layout2<__nv_bfloat16>(a_mn, b_mn, A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s);
+    if (out_fp32) return dispatch_layout2<float>(a_mn, b_mn, A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s, g);
+    return dispatch_layout2<__nv_bfloat16>(a_mn, b_mn, A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s, g);
   }
   int bn = tile_n;
   if (bn != 128 && bn != 256) {
@@ -579,9 +628,40 @@ LLMCTL_API int llmctl_gemm_bf16(const void* A, const void* B, void* C, int M, in
     bn = (c128 < c256) ? 128 : 256;
   }
   if (bn == 256) {
-    if (out_fp32) return dispatch_layout<256, float>(a_mn, b_mn, A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s);
-    return dispatch_layout<256, __nv_bfloat16>(a_mn, b_mn, A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s);
+    if (out_fp32) return dispatch_layout<256, float>(a_mn, b_mn, A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s, g);
+    return dispatch_layout<256, __nv_bfloat16>(a_mn, b_mn, A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s, g);
   }
-  if (out_fp32) return dispatch_layout<128, float>(a_mn, b_mn, A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s);
-  return dispatch_layout<128, __nv_bfloat16>(a_mn, b_mn, A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s);
+  if (out_fp32) return dispatch_layout<128, float>(a_mn, b_mn, A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s, g);
+  return dispatch_layout<128, __nv_bfloat16>(a_mn, b_mn, A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s, g);
+}
+
+LLMCTL_API int llmctl_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K,
+                                long long lda, long long ldb, long long ldc, int a_mn, int b_mn,
+                                int out_fp32, int beta, int tile_n, int max_ctas, void* stream) {
+  return gemm_bf16_impl(A, B, C, M, N, K, lda, ldb, ldc, a_mn, b_mn, out_fp32, beta, tile_n, max_ctas, stream,
+                        GemmGate{});
+}
+
+LLMCTL_SYMM_WATCHDOG_MODULE(gemm)
+
+// K1 consumer: the same GEMM, but rows of A (K-major, [M, K] in a symmetric buffer) outside [own_lo, own_hi) are only
+// read once their flag  flags[row / rows_per_flag]  (local signal pad, written by the peers' llmctl_ag_push) reached
+// `epoch`.  M = world * rows_per_rank; tile rows are visited in arrival order when the shapes allow it.
+LLMCTL_API int llmctl_gemm_bf16_gated(const void* A, const void* B, void* C, int M, int N, int K,
+                                      long long lda, long long ldb, long long ldc, int b_mn, int out_fp32,
+                                      int beta, int tile_n, int max_ctas, const unsigned int* flags,
+                                      unsigned int epoch, int rows_per_flag, int rank, int world,
+                                      void* stream) {
+  LLMCTL_REQUIRE(flags != nullptr && world >= 1 && world <= symm::kMaxRanks && M % world == 0 && rows_per_flag > 0 &&
+                 (M / world) % rows_per_flag == 0 && M / rows_per_flag <= 256);
+  GemmGate g{};
+  g.flags = flags;
+  g.epoch = epoch;
+  g.rows_per_flag = rows_per_flag;
+  g.own_lo = rank * (M / world);
+  g.own_hi = g.own_lo + M / world;
+  g.perm = 1;
+  g.rank = rank;
+  g.world = world;
+  return gemm_bf16_impl(A, B, C, M, N, K, lda, ldb, ldc, 0, b_mn, out_fp32, beta, tile_n, max_ctas, stream, g);
 }

@@ -48,7 +48,13 @@ struct Sched {
   bool fits(const Req& r) const {
     if (static_cast<int>(running.size()) >= max_batch_size) return false;
     if (reserved_tokens + reserve(r) > max_batch_tokens) return false;
-    if (kv && !llmctl_kv_can_allocate(kv, r.prompt_len + r.generated + 1)) return false;
+    if (kv && !llmctl_kv_can_allocate(kv, r.prompt_len + r.generated + 1)) {
+      // the watermark keeps head-room for running sequences to grow; with nothing running it would only starve a
+      // request that needs more than (total - watermark) blocks, so an empty engine admits on free blocks alone
+      const int bs = llmctl_kv_block_size(kv);
+      const int need = (r.prompt_len + r.generated + 1 + bs - 1) / bs;
+      if (!(running.empty() && llmctl_kv_free_blocks(kv) >= need)) return false;
+    }
     return true;
   }
 
@@ -179,6 +185,14 @@ API int llmctl_sched_on_token(void* h, long long id) {
       }
     }
     return 0;
+  }
+  // evicted earlier in this step (by another sequence's growth) after its logits were computed: the token it just
+  // produced is valid and must be counted, or re-admission would allocate one token too few
+  for (auto& r : s->waiting) {
+    if (r.id == id) {
+      r.generated += 1;
+      break;
+    }
   }
   return -1;
 }

@@ -26,33 +26,37 @@ from .symm import PeerTable, SymmBuffer
 _ctx: Optional["TPFusedContext"] = None
 
 vp, i32, i64, f32, u32 = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_float, ctypes.c_uint
-native.register_signature("llmctl_ag_gemm", [PeerTable, vp, vp, i32, i32, i32, i64, i64, PeerTable, vp, i32, i32, u32, i32, vp])
-native.register_signature("llmctl_gemm_rs", [vp, vp, PeerTable, i32, i32, i32, i64, i64, PeerTable, vp, i32, i32, u32, vp])
+native.register_signature("llmctl_ag_push", [vp, PeerTable, vp, i32, i32, i32, PeerTable, i32, i32, i32, u32, vp, i32, i32, vp])
+native.register_signature("llmctl_gemm_bf16_gated", [vp, vp, vp, i32, i32, i32, i64, i64, i64, i32, i32, i32, i32, i32, vp, u32,
+                                                     i32, i32, i32, vp])
+native.register_signature("llmctl_gemm_rs", [vp, vp, PeerTable, i32, i32, i32, i64, i64, i32, PeerTable, vp, i32, i32, u32, vp])
 native.register_signature("llmctl_rs_reduce_rmsnorm", [vp, PeerTable, i32, i32, vp, vp, vp, vp, vp, i32, i32, f32, u32, vp])
 native.register_signature("llmctl_ar_residual_rmsnorm", [PeerTable, i64, vp, PeerTable, i32, i32, i32, vp, vp, vp, vp, i32, i32, f32, u32, vp])
+
+K1_FLAG_BASE = 64          # signal-pad slots [64, 64 + world * slabs) of each Xg buffer: per-slab "rows arrived" flags
 
 
 class TPFusedContext:
     def __init__(self, group, rank: int, world: int, max_tokens: int, hidden: int, max_n: int, device: torch.device):
         self.group, self.rank, self.world, self.device = group, rank, world, device
         self.max_tokens, self.hidden = max_tokens, hidden
+        self.capacity = max_tokens * hidden
         # K1: gathered activations [M, K<=hidden]; K2: staging [world, M/world, N<=hidden]  (both M*hidden bf16)
-        self.xg = [SymmBuffer(max_tokens * hidden, torch.bfloat16, group, device) for _ in range(2)]
-        self.stage = [SymmBuffer(max_tokens * hidden, torch.bfloat16, group, device) for _ in range(2)]
-        self.flags_ag = torch.zeros(32, dtype=torch.int32, device=device)
+        self.xg = [SymmBuffer(self.capacity, torch.bfloat16, group, device) for _ in range(2)]
+        self.stage = [SymmBuffer(self.capacity, torch.bfloat16, group, device) for _ in range(2)]
+        self.push_counters = torch.zeros(64, dtype=torch.int32, device=device)
         self.flags_rs = torch.zeros(32, dtype=torch.int32, device=device)
-        # one epoch counter per kernel family (NOT per buffer): the local chunk_ready flags are shared by both
-        # alternating buffers, so epochs must keep increasing across them
+        # one epoch counter per kernel family (NOT per buffer): epochs keep increasing across the alternating buffers
         self.ep_ag = 0
         self.ep_rs = 0
         self.i_ag = 0
         self.i_rs = 0
-        self.n_copy = int(os.environ.get("LLMCTL_K1_COPY_CTAS", "0"))   # 0 = the kernel's default for this world size
+        self.use_multicast = os.environ.get("LLMCTL_K1_NVLS", "1") != "0"
+        self.calls = {"k1_fused": 0, "k1_nccl": 0, "k2_fused": 0}
         torch.cuda.synchronize(device)
         self.xg[0].barrier()
-        # K1 is only the default where it wins: at tp = 8 on this pool the gather of 7 remote shards is bound by
-        # NVLink read round trips and the fused kernel measured 165 us against 120 us for NCCL all-gather + GEMM,
-        # at tp = 2 it wins (82 vs 99 us).  LLMCTL_K1 = fused | nccl | auto (default: time both once, all ranks agree).
+        # LLMCTL_K1 = fused | nccl | auto (default: time both once at start-up, all ranks agree, outcome recorded in
+        # ``k1_timing`` and reported by bench.py)
         mode = os.environ.get("LLMCTL_K1", "auto").lower()
         self.k1_timing = None
         if mode == "fused" or world == 1:
@@ -62,15 +66,16 @@ class TPFusedContext:
         else:
             self.use_k1 = self._autotune_k1()
 
-    def _ag_gemm_nccl(self, x_local: torch.Tensor, w: torch.Tensor):
+    def _ag_gemm_nccl(self, x_local: torch.Tensor, w: torch.Tensor, w_mn: bool = False):
         Ms, K = x_local.shape
         full = torch.empty(Ms * self.world, K, dtype=x_local.dtype, device=x_local.device)
         dist.all_gather_into_tensor(full, x_local.contiguous(), group=self.group)
-        return ops.gemm_raw(full, w), full
+        self.calls["k1_nccl"] += 1
+        return ops.gemm_raw(full, w, b_mn=w_mn), full
 
     def _autotune_k1(self) -> bool:
         rows = max(min(self.max_tokens // self.world, 1024) // 8 * 8, 8)
-        K = self.hidden
+        K = min(self.hidden, 4096)
         N = max(min(self.hidden, 4096) // 8 * 8, 8)
         x = torch.randn(rows, K, device=self.device).bfloat16()
         w = torch.randn(N, K, device=self.device).bfloat16()
@@ -90,56 +95,73 @@ class TPFusedContext:
         t = torch.tensor(times, device=self.device)
         dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
         self.k1_timing = {"fused_ms": float(t[0]), "nccl_ms": float(t[1])}
+        self.calls = {k: 0 for k in self.calls}
         return bool(t[0] <= 1.02 * t[1])
 
-    def usable(self, x: torch.Tensor) -> bool:
-        return (ops.kernel_config().gemm == "native" and x.dim() == 2 and x.shape[0] * self.world <= self.max_tokens
-                and x.shape[1] <= self.hidden * 4)
+    def path_report(self) -> dict:
+        """Which transport the all-gather GEMMs took (for bench lines and logs)."""
+        return {"k1": "fused" if self.use_k1 else "nccl", "k1_autotune": self.k1_timing, "calls": dict(self.calls)}
+
+    # per-op gates on the real buffer requirement (the row-parallel input already has all M rows)
+    def usable_ag(self, x: torch.Tensor) -> bool:
+        return (ops.kernel_config().gemm == "native" and x.dim() == 2 and x.shape[1] % 8 == 0
+                and x.shape[0] * self.world * x.shape[1] <= self.capacity)
+
+    def usable_rs(self, x: torch.Tensor, n_out: int) -> bool:
+        return (ops.kernel_config().gemm == "native" and x.dim() == 2 and x.shape[0] % self.world == 0
+                and x.shape[0] * n_out <= self.capacity and n_out <= 8192)
 
     # ---- K1 ------------------------------------------------------------------------------------------
     def next_xg(self, rows_local: int, cols: int):
-        """The buffer the *producer* (norm) must write this rank's rows into for the next ag_linear."""
+        """The buffer the *producer* (norm) may write this rank's rows into for the next ag_linear."""
         buf = self.xg[self.i_ag]
         M = rows_local * self.world
         full = buf.tensor[:M * cols].view(M, cols)
         return buf, full, full[self.rank * rows_local:(self.rank + 1) * rows_local]
 
-    def ag_gemm(self, x_local: torch.Tensor, w: torch.Tensor):
-        """x_local [Ms, K] -> (y [M, N], Xg [M, K]): the fused kernel, or NCCL all-gather + tcgen05 GEMM where the
-        start-up measurement found that faster (see ``use_k1``)."""
+    def ag_gemm(self, x_local: torch.Tensor, w: torch.Tensor, w_mn: bool = False):
+        """x_local [Ms, K] -> (y [M, N], Xg [M, K]).  ``w`` is [N, K], or [K, N] with ``w_mn`` (a row-parallel forward
+        weight used untransposed for its dgrad).  Fused push + gated GEMM, or NCCL all-gather + GEMM where the start-up
+        measurement found that faster (see ``use_k1``)."""
         if not self.use_k1:
-            return self._ag_gemm_nccl(x_local, w)
-        return self._ag_gemm_fused(x_local, w)
+            return self._ag_gemm_nccl(x_local, w, w_mn)
+        return self._ag_gemm_fused(x_local, w, w_mn)
 
-    def _ag_gemm_fused(self, x_local: torch.Tensor, w: torch.Tensor):
-        """x_local [Ms, K] (copied into the symmetric buffer unless it already lives there) -> (y [M, N], Xg [M, K])."""
+    def _ag_gemm_fused(self, x_local: torch.Tensor, w: torch.Tensor, w_mn: bool = False):
         Ms, K = x_local.shape
-        N = w.shape[0]
+        N = w.shape[1] if w_mn else w.shape[0]
+        x_local = x_local if x_local.is_contiguous() else x_local.contiguous()
         buf, full, mine = self.next_xg(Ms, K)
-        if x_local.data_ptr() != mine.data_ptr():
-            mine.copy_(x_local)
         M = Ms * self.world
+        R = 256 if Ms % 256 == 0 else (128 if Ms % 128 == 0 else Ms)      # rows per arrival flag
+        while Ms // R > 32:
+            R *= 2
         self.ep_ag += 1
+        stream = native.stream_ptr()
+        mc = buf.multicast_ptr if self.use_multicast else 0
+        native.call("llmctl_ag_push", x_local.data_ptr(), buf.peers, mc or None, Ms, K, R, buf.pads, K1_FLAG_BASE, self.rank,
+                    self.world, self.ep_ag, self.push_counters.data_ptr(), int(x_local.data_ptr() == mine.data_ptr()), 0, stream)
         y = torch.empty(M, N, dtype=torch.bfloat16, device=x_local.device)
-        native.call("llmctl_ag_gemm", buf.peers, w.data_ptr(), y.data_ptr(), M, N, K, w.stride(0), y.stride(0),
-                    buf.pads, self.flags_ag.data_ptr(), self.rank, self.world, self.ep_ag, self.n_copy,
-                    native.stream_ptr())
+        native.call("llmctl_gemm_bf16_gated", full.data_ptr(), w.data_ptr(), y.data_ptr(), M, N, K, K, w.stride(0), N,
+                    int(w_mn), 0, 0, 0, 0, buf.signal_ptrs[self.rank] + 4 * K1_FLAG_BASE, self.ep_ag, R, self.rank, self.world,
+                    stream)
         self.i_ag ^= 1
+        self.calls["k1_fused"] += 1
         return y, full
 
     # ---- K2 ------------------------------------------------------------------------------------------
     def gemm_rs(self, x: torch.Tensor, w: torch.Tensor, residual: Optional[torch.Tensor] = None,
-                norm_w: Optional[torch.Tensor] = None, eps: float = 1e-5):
-        """x [M, Kl], w [N, Kl] -> reduce-scattered rows [M/world, N] (+ residual).  With ``norm_w`` also returns
-        rmsnorm(rows) * norm_w and rstd.  Returns (h, y, rstd)."""
+                norm_w: Optional[torch.Tensor] = None, eps: float = 1e-5, w_mn: bool = False):
+        """x [M, Kl], w [N, Kl] (or [Kl, N] with ``w_mn``) -> reduce-scattered rows [M/world, N] (+ residual).  With
+        ``norm_w`` also returns rmsnorm(rows) * norm_w and rstd.  Returns (h, y, rstd)."""
         M, Kl = x.shape
-        N = w.shape[0]
+        N = w.shape[1] if w_mn else w.shape[0]
         Ms = M // self.world
         buf = self.stage[self.i_rs]
         self.ep_rs += 1
         ep = self.ep_rs
-        native.call("llmctl_gemm_rs", x.data_ptr(), w.data_ptr(), buf.peers, M, N, Kl, x.stride(0), w.stride(0), buf.pads,
-                    self.flags_rs.data_ptr(), self.rank, self.world, ep, native.stream_ptr())
+        native.call("llmctl_gemm_rs", x.data_ptr(), w.data_ptr(), buf.peers, M, N, Kl, x.stride(0), w.stride(0), int(w_mn),
+                    buf.pads, self.flags_rs.data_ptr(), self.rank, self.world, ep, native.stream_ptr())
         h = torch.empty(Ms, N, dtype=torch.bfloat16, device=x.device)
         y = torch.empty_like(h) if norm_w is not None else None
         rstd = torch.empty(Ms, dtype=torch.float32, device=x.device) if norm_w is not None else None
@@ -147,6 +169,7 @@ class TPFusedContext:
                     native.ptr(residual), native.ptr(norm_w), h.data_ptr(), native.ptr(y), native.ptr(rstd), Ms, N,
                     float(eps), ep, native.stream_ptr())
         self.i_rs ^= 1
+        self.calls["k2_fused"] += 1
         return h, y, rstd
 
 
@@ -164,10 +187,8 @@ class _AGLinearFn(torch.autograd.Function):
     def backward(ctx, dy):
         xg, w = ctx.saved_tensors
         dy = dy if dy.is_contiguous() else dy.contiguous()
-        # dX_full = dy @ w  -> reduce-scatter over tokens.  K2 expects the weight as [N_out, K]: here the "weight"
-        # is w^T ([K_in, N_local]); use the transposed copy kept on the parameter (built lazily, refreshed per step)
-        wt = _transposed(w)
-        h, _, _ = _ctx.gemm_rs(dy, wt)
+        # dX_full = dy @ w -> reduce-scatter over tokens: K2 with the forward weight [N_local, K_in] read MN-major
+        h, _, _ = _ctx.gemm_rs(dy, w, w_mn=True)
         mg = getattr(w, "main_grad", None)
         if mg is not None:
             fresh = getattr(w, "_main_grad_fresh", False)
@@ -193,8 +214,7 @@ class _LinearRSFn(torch.autograd.Function):
     def backward(ctx, dh):
         x, w = ctx.saved_tensors
         dh = dh if dh.is_contiguous() else dh.contiguous()
-        wt = _transposed(w)                         # [K_local, N]: acts as the [N_out=K_local, K=N] weight of K1
-        dx, dh_full = _ctx.ag_gemm(dh, wt)
+        dx, dh_full = _ctx.ag_gemm(dh, w, w_mn=True)        # dX = all_gather(dh) @ w, w [N, K_local] read MN-major
         mg = getattr(w, "main_grad", None)
         if mg is not None:
             fresh = getattr(w, "_main_grad_fresh", False)
@@ -207,16 +227,6 @@ class _LinearRSFn(torch.autograd.Function):
         return dx, ops.gemm_raw(dh_full, x, a_mn=True, b_mn=True)
 
 
-def _transposed(w: torch.Tensor) -> torch.Tensor:
-    """w^T as a contiguous tensor, cached on the parameter and refreshed when the parameter version changes."""
-    from ..parallel.zero import PARAM_GENERATION
-    ver = (w._version, PARAM_GENERATION[0])
-    cached = getattr(w, "_wt_cache", None)
-    if cached is None or cached[0] != ver or cached[1].data_ptr() == 0:
-        w._wt_cache = (ver, w.detach().t().contiguous())
-    return w._wt_cache[1]
-
-
 def init_tp_workspace(max_tokens: int, hidden: int, max_n: Optional[int] = None) -> Optional[TPFusedContext]:
     """Create the fused TP/SP context for the current mesh (no-op unless CUDA + NCCL + tp > 1 + SP)."""
     global _ctx
@@ -226,7 +236,7 @@ def init_tp_workspace(max_tokens: int, hidden: int, max_n: Optional[int] = None)
     if st.tp <= 1 or not st.sequence_parallel or st.device.type != "cuda" or not symm.available():
         _ctx = None
         return None
-    if not native.has_symbol("llmctl_ag_gemm"):
+    if not native.has_symbol("llmctl_ag_push"):
         _ctx = None
         return None
     _ctx = TPFusedContext(st.tp_group, st.tp_rank, st.tp, max_tokens, hidden, max_n or hidden, st.device)
@@ -238,8 +248,16 @@ def shutdown() -> None:
     _ctx = None
 
 
-def enabled(x: torch.Tensor) -> bool:
-    return _ctx is not None and x.is_cuda and x.dtype == torch.bfloat16 and _ctx.usable(x)
+def enabled_ag(x: torch.Tensor) -> bool:
+    return _ctx is not None and x.is_cuda and x.dtype == torch.bfloat16 and _ctx.usable_ag(x)
+
+
+def enabled_rs(x: torch.Tensor, n_out: int) -> bool:
+    return _ctx is not None and x.is_cuda and x.dtype == torch.bfloat16 and _ctx.usable_rs(x, n_out)
+
+
+def path_report() -> Optional[dict]:
+    return _ctx.path_report() if _ctx is not None else None
 
 
 def ag_linear(x: torch.Tensor, w: torch.Tensor) -> torch.Tensor:

@@ -157,7 +157,7 @@ class ColumnParallelLinear(nn.Module):
         if st.tp > 1:
             if st.sequence_parallel:
                 from ..comms import fused
-                if fused.enabled(x):
+                if fused.enabled_ag(x):
                     return fused.ag_linear(x, self.weight)
                 x = gather_seq(x)
             else:
@@ -184,7 +184,7 @@ class RowParallelLinear(nn.Module):
         st = get_state()
         if st.tp > 1 and st.sequence_parallel:
             from ..comms import fused
-            if fused.enabled(x):
+            if fused.enabled_rs(x, self.weight.shape[0]):
                 return fused.linear_rs(x, self.weight)
         return self.finish(ops.linear(x, self.weight))
 

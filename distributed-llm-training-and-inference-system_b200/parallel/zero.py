@@ -86,6 +86,8 @@ class ParamUnit:
         else:
             flat = torch.zeros(self.numel, dtype=self.dtype, device=self.device)
         self._persistent_grad = grad_storage
+        self._grad_alloc: Optional[Callable[["ParamUnit"], torch.Tensor]] = None   # transient symmetric bucket (K7, ZeRO-2/3)
+        self._param_event = None      # K7: set while this unit's updated parameters are still being published
         for p, o in zip(self.params, self.offsets):
             flat[o:o + p.numel()].copy_(p.data.reshape(-1))
         self.flat_param: Optional[torch.Tensor] = flat
@@ -152,6 +154,8 @@ class ParamUnit:
         if self.flat_grad is None:
             if self._persistent_grad is not None:
                 self.flat_grad = self._persistent_grad[:self.numel]
+            elif self._grad_alloc is not None:
+                self.flat_grad = self._grad_alloc(self)
             else:
                 self.flat_grad = torch.empty(self.numel, dtype=self.grad_dtype, device=self.device)
             for lo, hi in self.gaps:
@@ -266,23 +270,27 @@ class ZeroOptimizer:
         named = [(n, m) for n, m in named if any(p.requires_grad for p in m.parameters())]
         self.units: List[ParamUnit] = []
         self.native_comm = self._init_native_comm(named, comm)
+        nc = self.native_comm
         off = 0
         for name, mod in named:
             ps = gs = None
-            if self.native_comm is not None:
+            if nc is not None:
                 n = _unit_numel(mod, self.st.dp)
-                ps = self.native_comm["params"].tensor[off:off + n]
-                gs = self.native_comm["grads"].tensor[off:off + n]
+                if nc["params"] is not None:
+                    ps = nc["params"].tensor[off:off + n]
+                if not nc["transient"]:
+                    gs = nc["grads"].tensor[off:off + n]
             u = ParamUnit(name, mod, self.st, self.zero_stage, self.grad_dtype, ps, gs)
             u._on_ready = self._unit_ready
             u.symm_off = off
-            if self.native_comm is not None:
+            if nc is not None:
                 off += u.numel
                 u.reduced = torch.empty(u.shard_numel, dtype=torch.float32, device=u.device)
+                if nc["transient"]:
+                    u._grad_alloc = self._alloc_transient_bucket
             self.units.append(u)
         self.gatherer = None
-        if (self.zero_stage >= 3 and self.st.dp > 1 and self.st.device.type == "cuda" and comm != "nccl"
-                and self.st.tp == 1 and self.st.pp == 1):
+        if self.zero_stage >= 3 and self.st.dp > 1 and self.st.device.type == "cuda" and comm != "nccl":
             try:
                 from ..comms import symm
                 from ..ops import functional as _ops
@@ -295,7 +303,15 @@ class ZeroOptimizer:
                     raise
                 self.gatherer = None
         self._last_micro = True
-        self.use_multicast = False       # NVLS multimem.st for the parameter push (opt-in after validation)
+        # NVLS: parameter push with one multimem.st per 16 bytes (bit-identical to the P2P push) and in-switch
+        # gradient reduction (fp32 accumulation, result rounded to bf16 like an NCCL bf16 reduce-scatter).
+        # LLMCTL_K7_NVLS=0 or deterministic mode selects P2P stores / rank-ordered fp32 pulls.
+        import os as _os
+        nvls = _os.environ.get("LLMCTL_K7_NVLS", "1") != "0"
+        self.use_multicast = nvls
+        self.use_nvls_reduce = nvls and _os.environ.get("LLMCTL_K7_NVLS_REDUCE", "1") != "0"
+        self.rs_ctas = int(_os.environ.get("LLMCTL_K7_RS_CTAS", "0"))
+        self.adam_ctas = int(_os.environ.get("LLMCTL_K7_ADAM_CTAS", "0"))
         self._norm_buf = None
         self.last_grad_norm: Optional[torch.Tensor] = None
         self._install_hooks()
@@ -304,6 +320,8 @@ class ZeroOptimizer:
     def _install_hooks(self) -> None:
         for u in self.units:
             u.module.register_full_backward_pre_hook(lambda m, g, u=u: self._pre_backward(u))
+            if self.native_comm is not None and self.native_comm["overlap_publish"]:
+                u.module.register_forward_pre_hook(lambda m, a, u=u: self._wait_unit(u))
             if self.zero_stage >= 3 and self.st.dp > 1:
                 u.module.register_forward_pre_hook(lambda m, a, u=u: u.gather_params())
                 u.module.register_forward_hook(lambda m, a, o, u=u: self._post_forward(u))
@@ -317,8 +335,24 @@ class ZeroOptimizer:
         if not torch.is_grad_enabled() or not getattr(self, "_in_backward", False):
             u.release_params()
 
+    def _wait_unit(self, u: ParamUnit) -> None:
+        """K7 publishes updated parameters unit by unit on a side stream; the first consumer waits here."""
+        ev = u._param_event
+        if ev is not None:
+            torch.cuda.current_stream(self.st.device).wait_event(ev)
+            u._param_event = None
+
+    def sync_params(self) -> None:
+        """Make the current stream wait until every unit's parameters are published (K7 side stream)."""
+        nc = self.native_comm
+        if nc is not None:
+            torch.cuda.current_stream(self.st.device).wait_stream(nc["stream"])
+            for u in self.units:
+                u._param_event = None
+
     def _pre_backward(self, u: ParamUnit) -> None:
         self._in_backward = True
+        self._wait_unit(u)
         if self.gatherer is not None:
             self.gatherer.direction = -1
         if self.zero_stage >= 3 and self.st.dp > 1:
@@ -481,31 +515,48 @@ class ZeroOptimizer:
 
     # ---- native (NVLink peer-memory) gradient / parameter path: K7 ---------------------------------
     def _init_native_comm(self, named, comm: str):
-        """Symmetric buffers for the fused reduce-scatter + AdamW + all-gather kernels.  Used when: CUDA,
-        dp > 1, ZeRO-1 (persistent buckets), bf16 gradients, no TP/PP sharing of the norm (tp == pp == 1)."""
+        """Symmetric buffers for the fused reduce-scatter + AdamW + all-gather kernels.  Used on CUDA with
+        dp > 1, ZeRO >= 1 and bf16 gradients, on any mesh (the DP group may be a sub-group of a TP/PP mesh).
+
+        ZeRO-1 keeps every unit's bucket in one persistent symmetric buffer; ZeRO-2/3 buckets are transient:
+        a small pool of symmetric slots (each as large as the biggest unit) is recycled through backward, a slot
+        being rewritten only after every rank announced that it finished reading the previous occupant.
+        ZeRO-3 has no replicated parameter buffer: AdamW writes the local parameter shard only."""
         st = self.st
-        if comm == "nccl" or st.dp <= 1 or st.device.type != "cuda" or self.zero_stage != 1:
+        if comm == "nccl" or st.dp <= 1 or st.device.type != "cuda" or self.zero_stage < 1:
             return None
-        if self.grad_dtype != torch.bfloat16 or st.tp != 1 or st.pp != 1:
+        if self.grad_dtype != torch.bfloat16:
             return None
         from ..ops import functional as ops
         if ops.kernel_config().optimizer != "native":
             return None
         try:
+            import os
             from ..comms import symm
             from ..ops import native
-            if not symm.available() or not native.has_symbol("llmctl_rs_sumsq"):
+            if not symm.available() or not native.has_symbol("llmctl_signal_wait"):
                 return None
-            total = sum(_unit_numel(m, st.dp) for _, m in named)
-            nc = {"params": symm.SymmBuffer(total, torch.bfloat16, st.dp_group, st.device),
-                  "grads": symm.SymmBuffer(total, torch.bfloat16, st.dp_group, st.device),
+            sizes = [_unit_numel(m, st.dp) for _, m in named]
+            total, biggest = sum(sizes), max(sizes)
+            transient = self.zero_stage >= 2
+            n_slots = max(2, int(os.environ.get("LLMCTL_ZERO_GRAD_SLOTS", "4"))) if transient else 0
+            nc = {"transient": transient, "n_slots": n_slots, "slot_numel": biggest,
+                  "params": symm.SymmBuffer(total, torch.bfloat16, st.dp_group, st.device) if self.zero_stage < 3 else None,
+                  "grads": symm.SymmBuffer(n_slots * biggest if transient else total, torch.bfloat16, st.dp_group, st.device),
                   "scalars": symm.SymmBuffer(64, torch.float32, st.dp_group, st.device),
-                  "stream": torch.cuda.Stream(device=st.device), "epoch_rs": 0, "epoch_step": 0,
+                  "stream": torch.cuda.Stream(device=st.device), "epoch_rs": 0, "epoch_step": 0, "epoch_end": 0,
                   "scratch": torch.empty(148 * 2, dtype=torch.float32, device=st.device),
-                  "norm": torch.zeros(1, dtype=torch.float32, device=st.device), "first_of_step": True}
+                  "norm": torch.zeros(1, dtype=torch.float32, device=st.device), "first_of_step": True,
+                  "free_slots": list(range(n_slots)), "slot_epoch": [0] * n_slots,
+                  # the norm needs contributions from TP / PP ranks too: computed by the generic path, handed
+                  # to the kernel as a device scalar
+                  "external_norm": st.tp > 1 or st.pp > 1,
+                  # publication of updated parameters overlaps the next forward (ZeRO-1/2 only: ZeRO-3 has no push)
+                  "overlap_publish": self.zero_stage < 3 and os.environ.get("LLMCTL_K7_OVERLAP", "1") != "0"}
+            nc["adam_pads"] = (nc["params"] or nc["scalars"]).pads
             nc["scalars"].tensor.zero_()
             torch.cuda.synchronize(st.device)
-            nc["params"].barrier()
+            nc["grads"].barrier()
             _register_k7_signatures()
             return nc
         except Exception as e:  # noqa: BLE001 - symmetric memory unavailable: NCCL path
@@ -515,6 +566,21 @@ class ZeroOptimizer:
             logging.getLogger("llmctl.zero").warning("native comm unavailable (%s: %s); using NCCL", type(e).__name__, e)
             return None
 
+    def _alloc_transient_bucket(self, u: ParamUnit) -> torch.Tensor:
+        """ZeRO-2/3 (K7): hand the unit a symmetric bucket slot.  Every rank walks backward in the same order, so
+        the slot choice agrees across ranks without communication."""
+        from ..ops import native
+        nc, st = self.native_comm, self.st
+        if not nc["free_slots"]:
+            raise RuntimeError("K7: all transient gradient slots are in use; raise LLMCTL_ZERO_GRAD_SLOTS")
+        s = nc["free_slots"].pop(0)                  # least recently released first: its pulls are long finished
+        u._slot = s
+        if nc["slot_epoch"][s] > 0:
+            native.call("llmctl_signal_wait", nc["grads"].pads, st.dp_rank, st.dp, 32 + 8 * s, nc["slot_epoch"][s],
+                        native.stream_ptr())
+        lo = s * nc["slot_numel"]
+        return nc["grads"].tensor[lo:lo + u.numel]
+
     def _reduce_unit_native(self, u: ParamUnit) -> None:
         from ..ops import native
         nc, st = self.native_comm, self.st
@@ -523,32 +589,78 @@ class ZeroOptimizer:
         ev.record(main)
         nc["stream"].wait_event(ev)
         nc["epoch_rs"] += 1
+        transient = nc["transient"]
+        if transient:
+            s = u._slot
+            off, done_slot = s * nc["slot_numel"], 32 + 8 * s
+            nc["slot_epoch"][s] += 1
+            done_epoch = nc["slot_epoch"][s]
+            accumulate_out = int(not getattr(u, "_shard_fresh", True))
+        else:
+            off, done_slot, done_epoch, accumulate_out = u.symm_off, -1, 0, 0
+        want_sumsq = self._last_micro and not nc["external_norm"]
+        mc = nc["grads"].multicast_ptr if self.use_nvls_reduce else 0
         with torch.cuda.stream(nc["stream"]):
-            native.call("llmctl_rs_sumsq", nc["grads"].peers, u.symm_off, nc["grads"].pads, st.dp_rank, st.dp,
-                        u.shard_lo, u.shard_numel, u.reduced.data_ptr(), nc["scratch"].data_ptr(),
-                        nc["scratch"].numel(), nc["scalars"].tensor.data_ptr(), int(not nc["first_of_step"]),
-                        nc["epoch_rs"], nc["stream"].cuda_stream)
-        nc["first_of_step"] = False
+            native.call("llmctl_rs_sumsq", nc["grads"].peers, off, (mc or None), nc["grads"].pads, st.dp_rank, st.dp,
+                        u.shard_lo, u.shard_numel, u.reduced.data_ptr(), accumulate_out, nc["scratch"].data_ptr(),
+                        nc["scratch"].numel(), nc["scalars"].tensor.data_ptr() if want_sumsq else None,
+                        int(not nc["first_of_step"]), nc["epoch_rs"], done_slot, done_epoch, self.rs_ctas,
+                        nc["stream"].cuda_stream)
+        if want_sumsq:
+            nc["first_of_step"] = False
         u.grad_shard = u.reduced
+        if transient:
+            u._shard_fresh = False
+            nc["free_slots"].append(s)
+            u.flat_grad = None
+            for p in u.params:
+                p.main_grad = None
 
     def _step_native(self, lr: float) -> torch.Tensor:
         from ..ops import native
         nc, st = self.native_comm, self.st
         main = torch.cuda.current_stream(st.device)
-        main.wait_stream(nc["stream"])
+        side = nc["stream"]
         self.step_count += 1
         nc["epoch_step"] += 1
         bc1 = 1.0 - self.betas[0] ** self.step_count
         bc2 = 1.0 - self.betas[1] ** self.step_count
         live = [u for u in self.units if u.grad_shard is not None]
-        mc = nc["params"].multicast_ptr if self.use_multicast else 0
-        for i, u in enumerate(live):
-            native.call("llmctl_adam_allgather", nc["params"].peers, u.symm_off, mc or None, nc["params"].pads,
-                        nc["scalars"].peers, st.dp_rank, st.dp, u.shard_lo, u.shard_numel, u.master.data_ptr(),
-                        u.exp_avg.data_ptr(), u.exp_avg_sq.data_ptr(), u.reduced.data_ptr(), lr, self.betas[0],
-                        self.betas[1], self.eps, self.weight_decay, bc1, bc2, 1.0 / st.dp,
-                        float(self.grad_clip or 0.0), nc["norm"].data_ptr(), nc["epoch_step"], int(i == 0),
-                        int(i == len(live) - 1), main.cuda_stream)
+        total_ptr = None
+        if nc["external_norm"]:
+            main.wait_stream(side)
+            self._sync_replicated_grads()
+            nc["total_sq"] = self.grad_norm_sq()          # reduced over DP, TP and PP; kept alive until the next step
+            total_ptr = nc["total_sq"].data_ptr()
+        overlap = nc["overlap_publish"]
+        push = int(nc["params"] is not None)
+        mc = nc["params"].multicast_ptr if (push and self.use_multicast) else 0
+        if overlap:
+            side.wait_stream(main)
+            stream = side
+        else:
+            main.wait_stream(side)
+            stream = main
+        with torch.cuda.stream(stream):
+            for i, u in enumerate(live):
+                nc["epoch_end"] += 1
+                local_out = u.param_shard.data_ptr() if (self.zero_stage >= 3 and u.param_shard is not None) else None
+                native.call("llmctl_adam_allgather", nc["params"].peers if push else nc["scalars"].peers, u.symm_off,
+                            mc or None, nc["adam_pads"], nc["scalars"].peers, total_ptr, st.dp_rank, st.dp, u.shard_lo,
+                            u.shard_numel, u.master.data_ptr(), u.exp_avg.data_ptr(), u.exp_avg_sq.data_ptr(),
+                            u.reduced.data_ptr(), local_out, push, lr, self.betas[0], self.betas[1], self.eps,
+                            self.weight_decay, bc1, bc2, 1.0 / st.dp, float(self.grad_clip or 0.0),
+                            nc["norm"].data_ptr(), nc["epoch_step"], int(i == 0 and (bool(push) or total_ptr is None)),
+                            nc["epoch_end"], push, self.adam_ctas, stream.cuda_stream)
+                if overlap:
+                    ev = torch.cuda.Event()
+                    ev.record(stream)
+                    u._param_event = ev
+        if overlap and live:
+            # after the first unit every rank has finished this step's pulls: the buckets may be rewritten and the
+            # gradient norm is final; later units are awaited by their first consumer (_wait_unit)
+            main.wait_event(live[0]._param_event)
+            live[0]._param_event = None
         nc["first_of_step"] = True
         self.last_grad_norm = nc["norm"]
         self.zero_grad()
@@ -556,6 +668,7 @@ class ZeroOptimizer:
 
     # ---- state dict (per-rank shard; see io/checkpoint.py) -------------------------------------
     def state_dict(self) -> Dict:
+        self.sync_params()
         return {
             "step": self.step_count,
             "zero_stage": self.zero_stage,
@@ -565,6 +678,7 @@ class ZeroOptimizer:
         }
 
     def load_state_dict(self, sd: Dict) -> None:
+        self.sync_params()
         self.step_count = int(sd["step"])
         for u in self.units:
             s = sd["units"][u.name]
@@ -579,6 +693,7 @@ class ZeroOptimizer:
         """Rewrite every compute-precision parameter from the fp32 master weights (all ranks must call it).  Used
         by the engine when a step produced non-finite values: the update was skipped, so the master copy is intact
         and a corrupted compute copy is healed by this."""
+        self.sync_params()
         with torch.no_grad():
             for u in self.units:
                 self._publish(u)
@@ -587,6 +702,7 @@ class ZeroOptimizer:
     def reset_from_params(self, step: int = 0) -> None:
         """Rebuild fp32 master weights from the current parameters and zero the moments (used when a
         checkpoint is resumed under a different plan, so the saved shards no longer line up)."""
+        self.sync_params()
         self.step_count = step
         with _FullParams(self):
             for u in self.units:
@@ -597,6 +713,9 @@ class ZeroOptimizer:
     def _publish(self, u: ParamUnit) -> None:
         """Write master weights back into the bf16 parameters (after a load)."""
         st = self.st
+        if self.native_comm is not None:
+            torch.cuda.current_stream(st.device).wait_stream(self.native_comm["stream"])
+            u._param_event = None
         if self.zero_stage >= 3 and st.dp > 1:
             u.param_shard.copy_(u.master)
             return
@@ -616,6 +735,7 @@ class _FullParams:
         self.opt = opt
 
     def __enter__(self):
+        self.opt.sync_params()
         for u in self.opt.units:
             if self.opt.zero_stage >= 3 and self.opt.st.dp > 1:
                 u.gather_params()
@@ -646,10 +766,12 @@ def _register_k7_signatures() -> None:
     from ..comms.symm import PeerTable
     from ..ops import native
     vp, i32, i64, f32, u32 = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_float, ctypes.c_uint
-    native.register_signature("llmctl_rs_sumsq", [PeerTable, i64, PeerTable, i32, i32, i64, i64, vp, vp, i32, vp, i32, u32, vp])
+    native.register_signature("llmctl_rs_sumsq", [PeerTable, i64, vp, PeerTable, i32, i32, i64, i64, vp, i32, vp, i32, vp, i32,
+                                                  u32, i32, u32, i32, vp])
+    native.register_signature("llmctl_signal_wait", [PeerTable, i32, i32, i32, u32, vp])
     native.register_signature("llmctl_adam_allgather",
-                              [PeerTable, i64, vp, PeerTable, PeerTable, i32, i32, i64, i64, vp, vp, vp, vp] + [f32] * 9 +
-                              [vp, u32, i32, i32, vp])
+                              [PeerTable, i64, vp, PeerTable, PeerTable, vp, i32, i32, i64, i64, vp, vp, vp, vp, vp, i32] +
+                              [f32] * 9 + [vp, u32, i32, u32, i32, i32, vp])
     _k7_registered = True
 
 

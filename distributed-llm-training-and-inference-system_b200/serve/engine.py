@@ -458,23 +458,29 @@ class InferenceEngine:
         self.stats["steps"] += 1
         finished: List[Sequence] = []
         decode = [self.seqs[r] for r, ph, _ in plan if ph == DECODE]
+        # A token's KV growth may evict other sequences of this very plan (their blocks are gone).  Evicted sequences
+        # are dropped from the rest of the step — unless their logits were already computed (batched decode), in
+        # which case the token is still emitted and the scheduler counts it for the later re-prefill.
+        evicted: set = set()
         # the sampled ids are read back in every phase (the step's only sync), so host clocks bracket device work
         t0 = time.perf_counter()
         for r, ph, _ in plan:
-            if ph == PREFILL:
+            if ph == PREFILL and r not in evicted:
                 s = self.seqs[r]
                 tok = self._sample(self._prefill(s), [s])[0]
                 self._emit(s, tok, finished)
+                evicted.update(self.sched.pop_preempted())
         t1 = time.perf_counter()
         self.stats["prefill_time_s"] += t1 - t0
+        decode = [s for s in decode if s.req_id not in evicted and not s.finished]
         if decode:
             toks = self._sample(self._decode(decode), decode)
             for s, tok in zip(decode, toks):
                 self._emit(s, tok, finished)
             self.stats["decode_time_s"] += time.perf_counter() - t1
             self.stats["decode_steps"] += 1
-        pre = self.sched.pop_preempted()
-        self.stats["preemptions"] += len(pre)
+        evicted.update(self.sched.pop_preempted())
+        self.stats["preemptions"] += len(evicted)
         return finished
 
     def _emit(self, s: Sequence, tok: int, finished: List[Sequence]) -> None:
@@ -515,8 +521,17 @@ class InferenceEngine:
     def generate(self, prompts: List[List[int]], max_tokens: int = 16, temperature: float = 0.0, top_p: float = 1.0,
                  top_k: int = -1) -> List[List[int]]:
         seqs = [self.add_request(p, max_tokens, temperature, top_p, top_k) for p in prompts]
+        idle = 0
         while any(not s.finished for s in seqs):
             if not self.has_work():
                 break
+            before = sum(len(s.generated) for s in seqs)
             self.step()
+            # a step that ran nothing while nothing is running means the queue cannot make progress any more
+            idle = idle + 1 if (sum(len(s.generated) for s in seqs) == before and self.sched.num_running == 0) else 0
+            if idle >= 3:
+                for s in seqs:
+                    if not s.finished:
+                        self.abort(s, "error")
+                break
         return [s.generated for s in seqs]

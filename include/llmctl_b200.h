@@ -142,30 +142,43 @@ int llmctl_allreduce_oneshot(llmctl_peer_table in, long long n, void* out, llmct
 int llmctl_allreduce_multimem(void* mc, long long n, llmctl_peer_table pads, int slot, int rank, int world,
                               unsigned int epoch, int max_ctas, void* stream);   /* NVLS multimem.ld_reduce/st */
 
-/* K1: all-gather (TMA bulk pulls by n_copy copy CTAs, 0 = default) fused with the column-parallel GEMM.
- * xg: symmetric [M,K]; local_flags: 32 zeroed uint32 in local memory. */
-int llmctl_ag_gemm(llmctl_peer_table xg, const void* W, void* C, int M, int N, int K, long long ldw, long long ldc,
-                   llmctl_peer_table pads, unsigned int* local_flags, int rank, int world, unsigned int epoch,
-                   int n_copy, void* stream);
+/* K1: sequence-parallel all-gather -> GEMM.  The owner pushes its rows into every rank's symmetric buffer
+ * (llmctl_ag_push: NVLS multimem.st when mc_xg != NULL, else P2P stores) slab by slab and raises per-slab epoch flags
+ * at pads[*][flag_base + row / rows_per_flag]; the consumer is the tcgen05 GEMM whose TMA producer waits per tile for
+ * the flags of the rows it reads (llmctl_gemm_bf16_gated; flags = this rank's pad + flag_base). counters: >= 32
+ * zeroed uint32 in local memory. */
+int llmctl_ag_push(const void* src, llmctl_peer_table xg, void* mc_xg, int rows, int cols, int rows_per_flag,
+                   llmctl_peer_table pads, int flag_base, int rank, int world, unsigned int epoch,
+                   unsigned int* counters, int src_in_xg, int max_ctas, void* stream);
+int llmctl_gemm_bf16_gated(const void* A, const void* B, void* C, int M, int N, int K, long long lda, long long ldb,
+                           long long ldc, int b_mn, int out_fp32, int beta, int tile_n, int max_ctas,
+                           const unsigned int* flags, unsigned int epoch, int rows_per_flag, int rank, int world,
+                           void* stream);
 /* K2: row-parallel GEMM whose epilogue pushes bf16 tiles into the owner's staging slot; finished by
  * llmctl_rs_reduce_rmsnorm (sum of the world slots + residual (+ RMSNorm)) on the sequence shard. */
 int llmctl_gemm_rs(const void* X, const void* W, llmctl_peer_table stage, int M, int N, int K, long long ldx,
-                   long long ldw, llmctl_peer_table pads, unsigned int* local_flags, int rank, int world,
-                   unsigned int epoch, void* stream);
+                   long long ldw, int w_mn /* W stored [K, N] */, llmctl_peer_table pads, unsigned int* local_flags,
+                   int rank, int world, unsigned int epoch, void* stream);
 int llmctl_rs_reduce_rmsnorm(const void* stage_local, llmctl_peer_table pads, int rank, int world,
                              const void* residual, const void* w, void* h_out, void* y, float* rstd, int rows,
                              int cols, float eps, unsigned int epoch, void* stream);
-/* K7: ZeRO gradient reduce-scatter (pull) + squared-norm partial, then AdamW on the shard + parameter
- * all-gather (push, or NVLS multimem.st when mc_params != NULL). */
-int llmctl_rs_sumsq(llmctl_peer_table grads, long long bucket_off, llmctl_peer_table pads, int rank, int world,
-                    long long shard_lo, long long shard_n, float* reduced, float* scratch, int scratch_elems,
-                    float* sumsq_out, int accumulate, unsigned int epoch, void* stream);
+/* K7: ZeRO gradient reduce-scatter of this rank's slice (in-switch multimem.ld_reduce when mc_grads != NULL,
+ * else rank-ordered P2P pull) + squared-norm partial; then AdamW on the shard + publication of the updated
+ * parameters (NVLS multimem.st when mc_params != NULL, else P2P stores; push = 0 writes local_out only).
+ * done_slot >= 0 announces "finished reading this bucket" to every rank; the bucket's next writer waits for it
+ * with llmctl_signal_wait (transient ZeRO-2/3 buckets). */
+int llmctl_rs_sumsq(llmctl_peer_table grads, long long bucket_off, const void* mc_grads, llmctl_peer_table pads,
+                    int rank, int world, long long shard_lo, long long shard_n, float* reduced, int accumulate_out,
+                    float* scratch, int scratch_elems, float* sumsq_out, int accumulate_sumsq, unsigned int epoch,
+                    int done_slot, unsigned int done_epoch, int max_ctas, void* stream);
+int llmctl_signal_wait(llmctl_peer_table pads, int rank, int world, int slot, unsigned int epoch, void* stream);
 int llmctl_adam_allgather(llmctl_peer_table params, long long bucket_off, void* mc_params, llmctl_peer_table pads,
-                          llmctl_peer_table scalars, int rank, int world, long long shard_lo, long long shard_n,
-                          float* master, float* m, float* v, const float* reduced, float lr, float beta1,
-                          float beta2, float eps, float weight_decay, float bias_corr1, float bias_corr2,
-                          float grad_scale, float max_norm, float* norm_out, unsigned int epoch,
-                          int begin_barrier, int end_barrier, void* stream);
+                          llmctl_peer_table scalars, const float* total_sq_dev, int rank, int world,
+                          long long shard_lo, long long shard_n, float* master, float* m, float* v,
+                          const float* reduced, void* local_out, int push, float lr, float beta1, float beta2,
+                          float eps, float weight_decay, float bias_corr1, float bias_corr2, float grad_scale,
+                          float max_norm, float* norm_out, unsigned int epoch_begin, int begin_barrier,
+                          unsigned int epoch_end, int end_barrier, int max_ctas, void* stream);
 /* K11: decode all-reduce of [rows, cols] partial sums + residual add + RMSNorm in one launch. */
 int llmctl_ar_residual_rmsnorm(llmctl_peer_table x, long long x_off, const void* mc_x, llmctl_peer_table pads,
                                int slot_base, int rank, int world, const void* residual, void* h_out,

@@ -42,7 +42,8 @@ void llmctl_sched_destroy(void* s);
 int llmctl_sched_add(void* s, long long id, int prompt_len, int max_tokens);
 /* Build the next step.  Fills parallel arrays; returns the number of entries (0 = nothing to run). */
 int llmctl_sched_step(void* s, long long* ids, int* phases, int* num_tokens, int max_out);
-/* Record that `id` produced one token in the last step (grows its KV allocation). 0 ok, -1 preempted. */
+/* Record that `id` produced one token in the last step (grows its KV allocation). 0 ok, -1 preempted (by this
+ * call, or earlier in the step: the token is still counted so that re-admission re-prefills prompt + generated). */
 int llmctl_sched_on_token(void* s, long long id);
 void llmctl_sched_finish(void* s, long long id);
 int llmctl_sched_num_waiting(void* s);

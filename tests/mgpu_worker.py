@@ -72,12 +72,16 @@ def case_tp_kernels(out, M=4096, K=4096, N=1536, Kl=1376):
         return g @ w.t()
     res["ag_gemm_ms"] = time_max(lambda: ctx._ag_gemm_fused(x_local, w))
     res["k1_autotune"] = {"use_k1": ctx.use_k1, "timing": ctx.k1_timing}
-    sweep = {}
-    for nc in (8, 16, 24, 32, 48):
-        ctx.n_copy = nc
-        sweep[str(nc)] = time_max(lambda: ctx._ag_gemm_fused(x_local, w))
-    ctx.n_copy = 0
-    res["ag_gemm_ms_by_copy_ctas"] = sweep
+    # MN-major weight (backward of a row-parallel layer): same product from w^T stored [K, N]
+    wt = w.t().contiguous()
+    y_mn, _ = ctx._ag_gemm_fused(x_local, wt, w_mn=True)
+    assert (y_mn.float() - ref).abs().max().item() / ref.abs().max().item() < 2e-2, "ag_gemm with MN-major weight"
+    if ctx.xg[0].multicast_ptr:
+        ctx.use_multicast = False
+        y_p2p, _ = ctx._ag_gemm_fused(x_local, w)
+        assert torch.equal(y_p2p, y), "P2P push differs from the NVLS push"
+        res["ag_gemm_p2p_push_ms"] = time_max(lambda: ctx._ag_gemm_fused(x_local, w))
+        ctx.use_multicast = True
     res["nccl_ag_then_cublas_ms"] = time_max(base_ag)
     res["gemm_only_cublas_ms"] = time_max(lambda: gathered @ w.t())
     # ---- K2 ----
@@ -98,6 +102,8 @@ def case_tp_kernels(out, M=4096, K=4096, N=1536, Kl=1376):
         e2 = (y2.float() - yref).abs().max().item()
         assert e1 < 2e-2 and e2 < 5e-2, f"gemm_rs errs {e1} {e2} on call {it}"
     res["gemm_rs_rel_err"] = e1
+    h_mn, _, _ = ctx.gemm_rs(x2, w2.t().contiguous(), residual=resid, w_mn=True)
+    assert (h_mn.float() - href).abs().max().item() / href.abs().max().item() < 2e-2, "gemm_rs with MN-major weight"
 
     def base_rs():
         p = x2 @ w2.t()
@@ -163,63 +169,143 @@ def _engine(kw, model=None):
     return eng
 
 
-def case_zero_native(out):
-    """K7: fused reduce-scatter + AdamW + all-gather vs the NCCL path, same init, 4 steps."""
+def case_k7_kernels(out):
+    """K7 against an fp32 PyTorch oracle, independent of the NCCL path: random per-rank gradients are written into the
+    buckets, reduced + clipped + AdamW-stepped by the fused kernels, and compared with all_reduce(fp32) + the AdamW
+    formula.  Covers ZeRO-1 (persistent buckets, parameter push) with NVLS and with P2P transport (the two pushes must
+    agree bit for bit), ZeRO-2 (transient bucket slots) and ZeRO-3 (local shard only), two steps each."""
+    import torch.nn as nn
+    from llmctl_b200.comms import mesh
     from llmctl_b200.parallel.zero import ZeroOptimizer
-    traj = {}
-    for comm in ("nccl", "native"):
-        eng = _engine(dict(zero_stage=1))
-        c = eng.config
-        eng.optimizer = ZeroOptimizer(eng.model, lr=c.learning_rate, betas=tuple(c.betas), eps=c.adam_eps, weight_decay=c.weight_decay,
-                                      zero_stage=1, grad_clip=c.gradient_clipping, state=eng.state, comm=comm)
-        from llmctl_b200.runtime.engine import LRSchedule
-        eng.scheduler = LRSchedule(c.learning_rate, 0, 100, "constant")
-        if comm == "native":
-            assert eng.optimizer.native_comm is not None, "native comm path was not enabled"
-        losses = []
-        for _ in range(4):
-            o = eng.train_step()
-            losses.append((eng._reduce_scalar(o["loss"]), float(o["grad_norm"])))
-        traj[comm] = losses
-        p0 = torch.cat([p.detach().float().reshape(-1)[:1000] for p in eng.model.parameters()])
-        traj[comm + "_p"] = p0
-        from llmctl_b200.comms import mesh
-        torch.cuda.synchronize(); dist.barrier()
+    world, rank = dist.get_world_size(), dist.get_rank()
+    res = {}
+    lr, b1, b2, eps, wd, clip = 1e-2, 0.9, 0.95, 1e-8, 0.1, 1.0
+    final = {}
+    for tag, stage, env in (("z1_nvls", 1, {}), ("z1_p2p", 1, {"LLMCTL_K7_NVLS": "0"}), ("z2", 2, {}), ("z3", 3, {}),
+                            ("z1_nvls_push_only", 1, {"LLMCTL_K7_NVLS_REDUCE": "0"})):
         mesh.reset_state()
-    for (la, ga), (lb, gb) in zip(traj["nccl"], traj["native"]):
-        assert abs(la - lb) < 2e-2 * max(1, abs(la)), f"loss nccl {traj['nccl']} native {traj['native']}"
-        assert abs(ga - gb) < 5e-2 * max(1, abs(ga)), f"gnorm nccl {traj['nccl']} native {traj['native']}"
-    dp = (traj["nccl_p"] - traj["native_p"]).abs().max().item()
-    assert dp < 5e-2, f"params diverged: {dp}"
-    out["zero_native"] = {"nccl": traj["nccl"], "native": traj["native"], "max_param_diff": dp}
+        st = mesh.init_mesh(dp=world)
+        for k in ("LLMCTL_K7_NVLS", "LLMCTL_K7_NVLS_REDUCE"):
+            os.environ.pop(k, None)
+        os.environ.update(env)
+        torch.manual_seed(5)
+        model = nn.Sequential(*[nn.Linear(512, 384 + 128 * i, bias=False) for i in range(5)]).cuda().bfloat16()
+        units = [(f"l{i}", m) for i, m in enumerate(model)]
+        opt = ZeroOptimizer(model, lr=lr, betas=(b1, b2), eps=eps, weight_decay=wd, zero_stage=stage, grad_clip=clip,
+                            units=units, state=st, comm="native")
+        assert opt.native_comm is not None, "K7 path not enabled"
+        # oracle state: fp32 master of the whole (unpadded) parameter set
+        with opt.full_params_context():
+            ref_p = [p.detach().float().clone() for p in model.parameters()]
+        ref_m = [torch.zeros_like(p) for p in ref_p]
+        ref_v = [torch.zeros_like(p) for p in ref_p]
+        errs = []
+        gen = torch.Generator(device="cuda").manual_seed(100 + rank)
+        for step in range(1, 3):
+            gsum = []
+            opt.set_micro_batch(0, 1)
+            for u in reversed(opt.units):                      # backward order
+                opt._pre_backward(u)
+                for p in u.params:
+                    g = torch.randn(p.shape, device="cuda", generator=gen) * (0.5 + rank)
+                    p.main_grad.copy_(g)
+                    gf = p.main_grad.float().clone()
+                    dist.all_reduce(gf)
+                    gsum.append((p, gf / world))
+                for p in u.params:
+                    u._param_grad_ready(p)
+            gmap = {id(p): g for p, g in gsum}
+            norm_ref = torch.sqrt(sum((g.double() ** 2).sum() for g in gmap.values())).float()
+            gn = opt.step(lr)
+            torch.cuda.synchronize()
+            coef = min(1.0, clip / (float(norm_ref) + 1e-6))
+            for i, p in enumerate(model.parameters()):
+                g = gmap[id(p)] * coef
+                ref_m[i] = b1 * ref_m[i] + (1 - b1) * g
+                ref_v[i] = b2 * ref_v[i] + (1 - b2) * g * g
+                mh, vh = ref_m[i] / (1 - b1 ** step), ref_v[i] / (1 - b2 ** step)
+                ref_p[i] = ref_p[i] * (1 - lr * wd) - lr * mh / (vh.sqrt() + eps)
+            assert abs(float(gn) - float(norm_ref)) < 1e-2 * float(norm_ref), f"{tag}: norm {float(gn)} vs {float(norm_ref)}"
+            with opt.full_params_context():
+                got = [p.detach().float().clone() for p in model.parameters()]
+            num = sum(((a - b.bfloat16().float()) ** 2).sum() for a, b in zip(got, ref_p)).sqrt().item()
+            den = sum((b ** 2).sum() for b in ref_p).sqrt().item()
+            upd = lr * sum(p.numel() for p in ref_p) ** 0.5        # size of one AdamW step (|m/sqrt(v)| ~ 1)
+            errs.append(num / upd)
+            assert num < 0.05 * upd, f"{tag} step {step}: parameter error {num} vs update size {upd}"
+        with opt.full_params_context():
+            flat = torch.cat([p.detach().reshape(-1) for p in model.parameters()]).clone()
+        ref = flat.clone(); dist.broadcast(ref, src=0)
+        assert torch.equal(flat, ref), f"{tag}: ranks hold different parameters"
+        final[tag] = flat
+        res[tag] = {"err_over_update": errs, "grad_norm": float(gn)}
+        torch.cuda.synchronize(); dist.barrier()
+    # the NVLS push must reproduce the P2P push exactly when the reduction is the same (rank-ordered pull)
+    assert torch.equal(final["z1_nvls_push_only"], final["z1_p2p"]), "multimem.st push differs from P2P push"
+    for k in ("LLMCTL_K7_NVLS", "LLMCTL_K7_NVLS_REDUCE"):
+        os.environ.pop(k, None)
+    mesh.reset_state()
+    out["k7_kernels"] = res
+
+
+def _zero_traj(stage, comm, steps=4):
+    from llmctl_b200.comms import mesh
+    from llmctl_b200.parallel.zero import ZeroOptimizer
+    from llmctl_b200.runtime.engine import LRSchedule
+    eng = _engine(dict(zero_stage=stage))
+    c = eng.config
+    eng.optimizer = ZeroOptimizer(eng.model, lr=c.learning_rate, betas=tuple(c.betas), eps=c.adam_eps, weight_decay=c.weight_decay,
+                                  zero_stage=stage, grad_clip=c.gradient_clipping, state=eng.state, comm=comm)
+    eng.scheduler = LRSchedule(c.learning_rate, 0, 100, "constant")
+    with eng.optimizer.full_params_context():
+        p_init = torch.cat([p.detach().float().reshape(-1) for p in eng.model.parameters()])
+    losses = []
+    for _ in range(steps):
+        o = eng.train_step()
+        losses.append((eng._reduce_scalar(o["loss"]), float(o["grad_norm"])))
+    with eng.optimizer.full_params_context():
+        p_end = torch.cat([p.detach().float().reshape(-1) for p in eng.model.parameters()])
+    info = {"native": eng.optimizer.native_comm is not None, "gatherer": eng.optimizer.gatherer is not None}
+    torch.cuda.synchronize(); dist.barrier()
+    mesh.reset_state()
+    return losses, p_end - p_init, info
+
+
+def _compare_zero(out, key, stage):
+    ref_l, ref_d, _ = _zero_traj(stage, "nccl")
+    nat_l, nat_d, info = _zero_traj(stage, "native")
+    assert info["native"], "K7 path was not enabled"
+    if stage >= 3:
+        assert info["gatherer"], "peer gatherer was not enabled"
+    for (la, ga), (lb, gb) in zip(ref_l, nat_l):
+        assert abs(la - lb) < 1e-2 * max(1, abs(la)), f"loss nccl {ref_l} native {nat_l}"
+        assert abs(ga - gb) < 2e-2 * max(1, abs(ga)), f"gnorm nccl {ref_l} native {nat_l}"
+    # gate relative to the size of the update itself: a path that skipped (or halved) the update fails
+    rel = ((nat_d - ref_d).norm() / ref_d.norm()).item()
+    assert ref_d.norm().item() > 0 and rel < 0.1, f"update differs from the NCCL path by {rel:.3f} of its size"
+    out[key] = {"nccl": ref_l, "native": nat_l, "update_rel_diff": rel}
+
+
+def case_zero_native(out):
+    """K7 in the engine (ZeRO-1): loss / grad-norm trajectory and the accumulated parameter update vs the NCCL path."""
+    _compare_zero(out, "zero_native", 1)
+
+
+def case_zero2_native(out):
+    _compare_zero(out, "zero2_native", 2)
 
 
 def case_zero3_native(out):
-    """K8 first step: ZeRO-3 with the peer-memory parameter gather (+prefetch) vs NCCL all-gathers."""
-    from llmctl_b200.parallel.zero import ZeroOptimizer
-    from llmctl_b200.runtime.engine import LRSchedule
-    traj = {}
-    for comm in ("nccl", "auto"):
-        eng = _engine(dict(zero_stage=3))
-        c = eng.config
-        eng.optimizer = ZeroOptimizer(eng.model, lr=c.learning_rate, betas=tuple(c.betas), eps=c.adam_eps, weight_decay=c.weight_decay,
-                                      zero_stage=3, grad_clip=c.gradient_clipping, state=eng.state, comm=comm)
-        eng.scheduler = LRSchedule(c.learning_rate, 0, 100, "constant")
-        if comm == "auto":
-            assert eng.optimizer.gatherer is not None, "peer gatherer was not enabled"
-        traj[comm] = [eng._reduce_scalar(eng.train_step()["loss"]) for _ in range(4)]
-        from llmctl_b200.comms import mesh
-        torch.cuda.synchronize(); dist.barrier()
-        mesh.reset_state()
-    for a, b in zip(traj["nccl"], traj["auto"]):
-        assert abs(a - b) < 2e-2 * max(1, abs(a)), f"{traj}"
-    out["zero3_native"] = traj
+    """ZeRO-3: K7 on transient buckets + peer-memory parameter gather (+prefetch) vs NCCL collectives."""
+    _compare_zero(out, "zero3_native", 3)
 
 
 def case_tp_sp_engine(out):
-    """TP=world + SP training with the fused K1/K2 linears vs the NCCL collectives."""
+    """TP=world + SP training with the fused K1/K2 linears (forced on, not auto-selected) vs the NCCL collectives;
+    the fused arm must really have launched K1 and K2 in forward and backward."""
     from llmctl_b200.comms import fused, mesh
     res = {}
+    os.environ["LLMCTL_K1"] = "fused"
     for mode in ("nccl", "fused"):
         eng = _engine(dict(tensor_parallel=dist.get_world_size(), sequence_parallel=True))
         if mode == "fused":
@@ -228,8 +314,14 @@ def case_tp_sp_engine(out):
             fused.shutdown()
         eng.setup_optimizer_and_scheduler()
         res[mode] = [eng._reduce_scalar(eng.train_step()["loss"]) for _ in range(4)]
+        if mode == "fused":
+            rep = fused.path_report()
+            res["paths"] = rep
+            # per step and layer: 2 K1 + 2 K2 forward, 2 K1 + 2 K2 backward
+            assert rep["calls"]["k1_fused"] >= 4 * 2 * 4 and rep["calls"]["k2_fused"] >= 4 * 2 * 4 and rep["calls"]["k1_nccl"] == 0, rep
         torch.cuda.synchronize(); dist.barrier()
         fused.shutdown(); mesh.reset_state()
+    os.environ.pop("LLMCTL_K1", None)
     for a, b in zip(res["nccl"], res["fused"]):
         assert abs(a - b) < 3e-2 * max(1, abs(a)), f"{res}"
     out["tp_sp_engine"] = res
@@ -328,7 +420,8 @@ def case_tp_serving(out):
     out["tp_serving"] = res
 
 
-CASES = {"tp_serving": case_tp_serving, "watchdog": case_watchdog, "probe": case_probe, "tp_kernels": case_tp_kernels, "zero_native": case_zero_native, "zero3_native": case_zero3_native,
+CASES = {"tp_serving": case_tp_serving, "watchdog": case_watchdog, "probe": case_probe, "tp_kernels": case_tp_kernels, "k7_kernels": case_k7_kernels, "zero_native": case_zero_native, "zero2_native": case_zero2_native,
+         "zero3_native": case_zero3_native,
          "tp_sp_engine": case_tp_sp_engine}
 
 

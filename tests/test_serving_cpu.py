@@ -116,6 +116,42 @@ def test_engine_continuous_batching_under_pressure():
     assert too_big.finished and too_big.finish_reason == "error"
 
 
+def test_engine_preemption_under_kv_pressure_matches_full_recompute():
+    """Eight KV blocks of four tokens for four requests that each need four: growth evicts running sequences in the
+    middle of a step (both from the prefill phase and inside the batched decode).  Evicted sequences are re-prefilled
+    over prompt + generated tokens and every output must still equal greedy decoding by full recompute."""
+    from llmctl_b200.comms import mesh
+    from llmctl_b200.serve.engine import InferenceEngine
+    mesh.reset_state()
+    torch.manual_seed(0)
+    eng = InferenceEngine("gpt-tiny", device="cpu", kv_block_size=4, num_kv_blocks=8, max_batch_size=4,
+                          max_batch_tokens=512, scheduler="vllm-like")
+    prompts = [[5, 9, 200, 31], [8, 8, 100], [300, 2, 3, 4, 5], [17, 18]]
+    outs = eng.generate(prompts, max_tokens=12, temperature=0.0)
+    assert eng.stats["preemptions"] >= 1, "the test did not create KV pressure"
+    assert all(len(o) == 12 for o in outs), [len(o) for o in outs]
+    for p, o in zip(prompts, outs):
+        ids = list(p)
+        for t in o:
+            logits = eng.model(torch.tensor([ids])).float()[-1, :eng.cfg.vocab_size]
+            assert int(logits.argmax()) == t
+            ids.append(t)
+    assert eng.kv.free_blocks == 8 and not eng.has_work()
+
+
+def test_request_larger_than_the_watermarked_pool_is_not_starved():
+    """A request that needs more blocks than (total - watermark) is admitted once the engine is empty instead of
+    waiting forever; generate() terminates either way."""
+    from llmctl_b200.comms import mesh
+    from llmctl_b200.serve.engine import InferenceEngine
+    mesh.reset_state()
+    torch.manual_seed(0)
+    eng = InferenceEngine("gpt-tiny", device="cpu", kv_block_size=4, num_kv_blocks=8, max_batch_size=2,
+                          max_batch_tokens=512, scheduler="vllm-like")
+    out = eng.generate([list(range(3, 3 + 26))], max_tokens=5, temperature=0.0)      # 31 tokens = 8 blocks = whole pool
+    assert len(out[0]) == 5 and not eng.has_work()
+
+
 def test_scheduler_plugin_orders_admission():
     """A registered scheduler plugin (``schedule(requests) -> ordered requests``) decides which waiting request the
     native continuous-batching core sees first; budgets and KV accounting stay native."""
