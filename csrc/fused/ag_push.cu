@@ -33,24 +33,33 @@ ag_push_kernel(const uint4* __restrict__ src, uint4* __restrict__ mc_dst, PeerTa
     const long long base = dst_off_vec + sl * slab_vec;
     long long v = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
     if (mc_dst != nullptr) {
-      for (; v + stride < slab_vec; v += 2 * stride) {
-        const uint4 a = s_src[v], b = s_src[v + stride];
-        ptx::multimem_st_v4(mc_dst + base + v, a);
-        ptx::multimem_st_v4(mc_dst + base + v + stride, b);
+      for (; v + 7 * stride < slab_vec; v += 8 * stride) {       // 8 independent 16-byte loads in flight per thread
+        uint4 a[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) a[u] = s_src[v + u * stride];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) ptx::multimem_st_v4(mc_dst + base + v + u * stride, a[u]);
       }
       for (; v < slab_vec; v += stride) ptx::multimem_st_v4(mc_dst + base + v, s_src[v]);
     } else {
-      for (; v < slab_vec; v += stride) {
-        const uint4 a = s_src[v];
+      auto put = [&](long long at, const uint4& a) {
 #pragma unroll
         for (int i = 0; i < kMaxRanks; ++i) {
           if (i < world) {
             const int dst = (rank + i) % world;       // staggered: no egress hot-spot
             if (dst == rank && skip_self) continue;
-            ptx::st_v4(reinterpret_cast<uint4*>(peers.ptr[dst]) + base + v, a);
+            ptx::st_v4(reinterpret_cast<uint4*>(peers.ptr[dst]) + base + at, a);
           }
         }
+      };
+      for (; v + 3 * stride < slab_vec; v += 4 * stride) {
+        uint4 a[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) a[u] = s_src[v + u * stride];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) put(v + u * stride, a[u]);
       }
+      for (; v < slab_vec; v += stride) put(v, s_src[v]);
     }
     // slab complete on this CTA -> the last CTA to get here raises the slab's flag on every rank
     __threadfence_system();
@@ -97,4 +106,55 @@ LLMCTL_API int llmctl_ag_push(const void* src, llmctl::symm::PeerTable xg, void*
       (const uint4*)src, (uint4*)mc_xg, xg, dst_off_vec, slab_vec, n_slabs, pads, flag_base, rank * n_slabs, rank,
       world, epoch, counters, src_in_xg);
   LLMCTL_RETURN_LAST();
+}
+
+extern "C" int llmctl_gemm_bf16_gated(const void* A, const void* B, void* C, int M, int N, int K, long long lda,
+                                      long long ldb, long long ldc, int b_mn, int out_fp32, int beta, int tile_n,
+                                      int max_ctas, const unsigned int* flags, unsigned int epoch,
+                                      int rows_per_flag, int rank, int world, void* stream);
+
+namespace {
+struct ForkJoinEvents {
+  cudaEvent_t ready = nullptr, pushed = nullptr;
+};
+ForkJoinEvents g_fj[64];
+}  // namespace
+
+// K1 in one call: Y[M, N] = all_gather(X rows)[M, K] * W^T.  This rank's rows must already sit in its block of the
+// local symmetric buffer (xg.ptr[rank] + rank*rows*K).  The push runs on `push_stream`, forked from / joined to
+// `stream` with events, so it overlaps the GEMM's work on the local rows; the GEMM consumes remote slabs as their
+// flags arrive.  W: [N, K] (ldw) or, with w_mn, stored [K, N].  tile_n as in llmctl_gemm_bf16 (the time between the
+// last slab's arrival and the end of the kernel is one tile, so smaller tiles shorten the un-overlapped tail).
+// The first call on a device creates two events.
+LLMCTL_API int llmctl_ag_gemm(llmctl::symm::PeerTable xg, void* mc_xg, const void* W, void* Y, int M, int N, int K,
+                              long long ldw, long long ldy, int w_mn, int rows_per_flag,
+                              llmctl::symm::PeerTable pads, int flag_base, int rank, int world, unsigned int epoch,
+                              unsigned int* counters, int push_ctas, int tile_n, void* push_stream, void* stream) {
+  LLMCTL_BEGIN();
+  LLMCTL_REQUIRE(world >= 1 && world <= symm::kMaxRanks && M % world == 0);
+  int dev = 0;
+  LLMCTL_CHECK(cudaGetDevice(&dev));
+  LLMCTL_REQUIRE(dev >= 0 && dev < 64);
+  ForkJoinEvents& fj = g_fj[dev];
+  if (fj.ready == nullptr) {
+    LLMCTL_CHECK(cudaEventCreateWithFlags(&fj.ready, cudaEventDisableTiming));
+    LLMCTL_CHECK(cudaEventCreateWithFlags(&fj.pushed, cudaEventDisableTiming));
+  }
+  cudaStream_t main_s = (cudaStream_t)stream, side = (cudaStream_t)push_stream;
+  const int rows = M / world;
+  const __nv_bfloat16* mine = reinterpret_cast<const __nv_bfloat16*>(xg.ptr[rank]) + static_cast<long long>(rank) * rows * K;
+  if (world > 1) {
+    LLMCTL_CHECK(cudaEventRecord(fj.ready, main_s));
+    LLMCTL_CHECK(cudaStreamWaitEvent(side, fj.ready, 0));
+    int rc = llmctl_ag_push(mine, xg, mc_xg, rows, K, rows_per_flag, pads, flag_base, rank, world, epoch, counters, 1,
+                            push_ctas, side);
+    if (rc) return rc;
+    LLMCTL_CHECK(cudaEventRecord(fj.pushed, side));
+  }
+  int rc = llmctl_gemm_bf16_gated(xg.ptr[rank], W, Y, M, N, K, K, ldw, ldy, w_mn, 0, 0, tile_n, 0,
+                                  reinterpret_cast<const unsigned int*>(pads.ptr[rank]) + flag_base, epoch,
+                                  rows_per_flag, rank, world, stream);
+  if (rc) return rc;
+  if (world > 1) LLMCTL_CHECK(cudaStreamWaitEvent(main_s, fj.pushed, 0));   // buffer reuse: our own push is over
+  return 0;
 }

@@ -275,7 +275,7 @@ LLMCTL_API int llmctl_rs_sumsq(llmctl::symm::PeerTable grads, long long bucket_o
                  bucket_off % 8 == 0 && scratch_elems >= 1 && done_slot < 480);
   cudaStream_t s = (cudaStream_t)stream;
   long long blocks = ((shard_n >> 3) + 255) / 256;
-  if (max_ctas <= 0) max_ctas = mc_grads ? 48 : kNumSMs * 2;
+  if (max_ctas <= 0) max_ctas = mc_grads ? 128 : kNumSMs * 2;
   if (blocks < 1) blocks = 1;
   if (blocks > max_ctas) blocks = max_ctas;
   if (blocks > scratch_elems) blocks = scratch_elems;

@@ -27,6 +27,8 @@ _ctx: Optional["TPFusedContext"] = None
 
 vp, i32, i64, f32, u32 = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_float, ctypes.c_uint
 native.register_signature("llmctl_ag_push", [vp, PeerTable, vp, i32, i32, i32, PeerTable, i32, i32, i32, u32, vp, i32, i32, vp])
+native.register_signature("llmctl_ag_gemm", [PeerTable, vp, vp, vp, i32, i32, i32, i64, i64, i32, i32, PeerTable, i32, i32, i32, u32, vp,
+                                             i32, i32, vp, vp])
 native.register_signature("llmctl_gemm_bf16_gated", [vp, vp, vp, i32, i32, i32, i64, i64, i64, i32, i32, i32, i32, i32, vp, u32,
                                                      i32, i32, i32, vp])
 native.register_signature("llmctl_gemm_rs", [vp, vp, PeerTable, i32, i32, i32, i64, i64, i32, PeerTable, vp, i32, i32, u32, vp])
@@ -52,6 +54,11 @@ class TPFusedContext:
         self.i_ag = 0
         self.i_rs = 0
         self.use_multicast = os.environ.get("LLMCTL_K1_NVLS", "1") != "0"
+        # the push runs on its own stream, concurrently with the GEMM's work on the rows this rank already holds
+        self.push_stream = torch.cuda.Stream(device=device)
+        self.push_ctas = int(os.environ.get("LLMCTL_K1_PUSH_CTAS", "32"))
+        self.tile_n = int(os.environ.get("LLMCTL_K1_TILE", "0"))            # 0 auto, 2 pair tile, 256 / 128 single-CTA tiles
+        self.slab_rows = int(os.environ.get("LLMCTL_K1_SLAB_ROWS", "256"))
         self.calls = {"k1_fused": 0, "k1_nccl": 0, "k2_fused": 0}
         torch.cuda.synchronize(device)
         self.xg[0].barrier()
@@ -133,18 +140,18 @@ class TPFusedContext:
         x_local = x_local if x_local.is_contiguous() else x_local.contiguous()
         buf, full, mine = self.next_xg(Ms, K)
         M = Ms * self.world
-        R = 256 if Ms % 256 == 0 else (128 if Ms % 128 == 0 else Ms)      # rows per arrival flag
+        R = self.slab_rows if Ms % self.slab_rows == 0 else (128 if Ms % 128 == 0 else Ms)   # rows per arrival flag
         while Ms // R > 32:
             R *= 2
         self.ep_ag += 1
-        stream = native.stream_ptr()
         mc = buf.multicast_ptr if self.use_multicast else 0
-        native.call("llmctl_ag_push", x_local.data_ptr(), buf.peers, mc or None, Ms, K, R, buf.pads, K1_FLAG_BASE, self.rank,
-                    self.world, self.ep_ag, self.push_counters.data_ptr(), int(x_local.data_ptr() == mine.data_ptr()), 0, stream)
+        if x_local.data_ptr() != mine.data_ptr():
+            mine.copy_(x_local)               # the GEMM reads this rank's rows from the local buffer right away
         y = torch.empty(M, N, dtype=torch.bfloat16, device=x_local.device)
-        native.call("llmctl_gemm_bf16_gated", full.data_ptr(), w.data_ptr(), y.data_ptr(), M, N, K, K, w.stride(0), N,
-                    int(w_mn), 0, 0, 0, 0, buf.signal_ptrs[self.rank] + 4 * K1_FLAG_BASE, self.ep_ag, R, self.rank, self.world,
-                    stream)
+        # one call: push on the side stream (forked / joined with events inside) + flag-gated GEMM on this stream
+        native.call("llmctl_ag_gemm", buf.peers, mc or None, w.data_ptr(), y.data_ptr(), M, N, K, w.stride(0), N, int(w_mn), R,
+                    buf.pads, K1_FLAG_BASE, self.rank, self.world, self.ep_ag, self.push_counters.data_ptr(), self.push_ctas,
+                    self.tile_n, self.push_stream.cuda_stream, native.stream_ptr())
         self.i_ag ^= 1
         self.calls["k1_fused"] += 1
         return y, full

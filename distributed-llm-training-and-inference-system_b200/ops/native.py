@@ -111,7 +111,7 @@ class NativeError(RuntimeError):
 
 #: kernels launched per entry point when it is not exactly one
 _KERNELS_PER_CALL = {"llmctl_rmsnorm_bwd": 2, "llmctl_layernorm_bwd": 3, "llmctl_sumsq": 2, "llmctl_rmsnorm_bwd_noalloc": 2,
-                     "llmctl_flash_attn_bwd": 3, "llmctl_rs_sumsq": 2, "llmctl_paged_attn_decode": 2,
+                     "llmctl_flash_attn_bwd": 3, "llmctl_rs_sumsq": 2, "llmctl_ag_gemm": 2, "llmctl_paged_attn_decode": 2,
                      "llmctl_comm_watchdog_poll": 0, "llmctl_comm_watchdog_set_timeout_ms": 0}
 
 

@@ -134,9 +134,11 @@ class ParamUnit:
         if self.flat_param is not None:
             return
         gatherer = getattr(self, "_gatherer", None)
-        if gatherer is not None:
+        if gatherer is not None and (gatherer.free or self.name in gatherer.owner):
             flat = gatherer.gather(self)
         else:
+            # no peer-memory pool, or every pool buffer is taken (a full-model gather for a checkpoint / export keeps
+            # all units resident at once): plain all-gather into ordinary memory
             flat = torch.empty(self.numel, dtype=self.dtype, device=self.device)
             dist.all_gather_into_tensor(flat, self.param_shard, group=self.st.dp_group)
         self.flat_param = flat

@@ -147,6 +147,10 @@ int llmctl_allreduce_multimem(void* mc, long long n, llmctl_peer_table pads, int
  * at pads[*][flag_base + row / rows_per_flag]; the consumer is the tcgen05 GEMM whose TMA producer waits per tile for
  * the flags of the rows it reads (llmctl_gemm_bf16_gated; flags = this rank's pad + flag_base). counters: >= 32
  * zeroed uint32 in local memory. */
+int llmctl_ag_gemm(llmctl_peer_table xg, void* mc_xg, const void* W, void* Y, int M, int N, int K, long long ldw,
+                   long long ldy, int w_mn, int rows_per_flag, llmctl_peer_table pads, int flag_base, int rank,
+                   int world, unsigned int epoch, unsigned int* counters, int push_ctas, int tile_n,
+                   void* push_stream, void* stream);   /* push (side stream) + gated GEMM in one call */
 int llmctl_ag_push(const void* src, llmctl_peer_table xg, void* mc_xg, int rows, int cols, int rows_per_flag,
                    llmctl_peer_table pads, int flag_base, int rank, int world, unsigned int epoch,
                    unsigned int* counters, int src_in_xg, int max_ctas, void* stream);

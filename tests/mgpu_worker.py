@@ -27,6 +27,18 @@ def time_max(fn, iters=10, warm=3):
     return float(t)
 
 
+def cpu_us(fn, iters=20):
+    """Host time to enqueue one call (the GPU is drained first, so this is pure launch cost)."""
+    import time
+    torch.cuda.synchronize(); dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(iters):
+        fn()
+    t = (time.perf_counter() - t0) / iters * 1e6
+    torch.cuda.synchronize()
+    return t
+
+
 def case_probe(out):
     from llmctl_b200.comms import symm
     buf = symm.SymmBuffer(1 << 20, torch.bfloat16)
@@ -45,6 +57,7 @@ def case_tp_kernels(out, M=4096, K=4096, N=1536, Kl=1376):
     from llmctl_b200.comms import fused
     from llmctl_b200.comms.mesh import init_mesh
     from llmctl_b200.ops import native
+    from llmctl_b200.ops.functional import gemm_raw as ops_gemm
     st = init_mesh(tp=dist.get_world_size(), sequence_parallel=True)
     ctx = fused.init_tp_workspace(max_tokens=M, hidden=4096)
     assert ctx is not None, "fused TP context unavailable"
@@ -70,7 +83,42 @@ def case_tp_kernels(out, M=4096, K=4096, N=1536, Kl=1376):
         g = torch.empty(M, K, device="cuda", dtype=torch.bfloat16)
         dist.all_gather_into_tensor(g, x_local)
         return g @ w.t()
-    res["ag_gemm_ms"] = time_max(lambda: ctx._ag_gemm_fused(x_local, w))
+    res["ag_gemm_ms"] = time_max(lambda: ctx._ag_gemm_fused(x_local, w), iters=30)
+    res["ag_gemm_enqueue_us"] = cpu_us(lambda: ctx._ag_gemm_fused(x_local, w))
+    res["nccl_ag_then_cublas_enqueue_us"] = cpu_us(base_ag)
+    # the two halves on their own: push without a consumer, GEMM with every flag already raised
+    from llmctl_b200.comms.fused import K1_FLAG_BASE
+    buf = ctx.xg[0]
+    mine = buf.tensor[:M * K].view(M, K)[r * Ms:(r + 1) * Ms]
+
+    def push_only(ctas, R, mc=True):
+        def f():
+            ctx.ep_ag += 1
+            native.call("llmctl_ag_push", mine.data_ptr(), buf.peers, (buf.multicast_ptr or None) if mc else None, Ms, K, R,
+                        buf.pads, K1_FLAG_BASE, r, W, ctx.ep_ag, ctx.push_counters.data_ptr(), 1, ctas, native.stream_ptr())
+        return f
+    parts = {}
+    for ctas in (16, 32, 64, 148):
+        for R in sorted({min(256, Ms), Ms}):
+            parts[f"push_ctas{ctas}_R{R}_us"] = 1e3 * time_max(push_only(ctas, R), iters=20)
+    parts["push_p2p_ctas64_us"] = 1e3 * time_max(push_only(64, min(256, Ms), mc=False), iters=20)
+    yy = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+
+    def gemm_only():
+        native.call("llmctl_gemm_bf16_gated", buf.tensor.data_ptr(), w.data_ptr(), yy.data_ptr(), M, N, K, K, w.stride(0), N,
+                    0, 0, 0, 0, 0, buf.signal_ptrs[r] + 4 * K1_FLAG_BASE, 1, min(256, Ms), r, W, native.stream_ptr())
+    parts["gated_gemm_flags_set_us"] = 1e3 * time_max(gemm_only, iters=20)
+    parts["plain_gemm_native_us"] = 1e3 * time_max(lambda: ops_gemm(gathered, w), iters=20)
+    res["k1_parts"] = parts
+    sweep = {}
+    for tile in (2, 256, 128):
+        for slab in sorted({128, 256, Ms}):
+            if Ms % slab:
+                continue
+            ctx.tile_n, ctx.slab_rows = tile, slab
+            sweep[f"tile{tile}_slab{slab}"] = time_max(lambda: ctx._ag_gemm_fused(x_local, w), iters=20)
+    ctx.tile_n, ctx.slab_rows = 0, 256
+    res["ag_gemm_ms_sweep"] = sweep
     res["k1_autotune"] = {"use_k1": ctx.use_k1, "timing": ctx.k1_timing}
     # MN-major weight (backward of a row-parallel layer): same product from w^T stored [K, N]
     wt = w.t().contiguous()
