@@ -177,7 +177,7 @@ def run(args) -> dict:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     dev_ms, wall_ms = float(ms[0]) / K, float(ms[1]) / K
     tokens = args.micro_batch * args.seq_len * world
-    res = {"metric": "train tokens/sec (GPT-7B)", "value": tokens / (dev_ms / 1e3), "unit": "tokens/s", "n_gpus": world, "steps": K,
+    res = {"metric": f"train tokens/sec ({args.model.upper()})", "value": tokens / (dev_ms / 1e3), "unit": "tokens/s", "n_gpus": world, "steps": K,
            "warmup": W, "ms_per_step": dev_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
            "data": "synthetic tokens, random-init weights", "impl": "reference",
            "note": "unmodified reference (baseline/_ref) through TrainingEngine.train(); import shims for the absent "

@@ -50,6 +50,9 @@ def parse_args():
     ap.add_argument("--activation-checkpoint", default="none")
     ap.add_argument("--grad-accum", type=int, default=None, help="micro-batches per step (default 1; 2*pp with a pipeline)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="8 GPUs: skip the TP8+SP / ZeRO-3 / 13B TP4xPP2 arms")
+    ap.add_argument("--extra-steps", type=int, default=20)
+    ap.add_argument("--extras-budget-s", type=float, default=420.0)
     ap.add_argument("--gemm", default=None, help="override GEMM backend: native|cublas")
     ap.add_argument("--attention", default=None, help="override attention backend: native|sdpa")
     return ap.parse_args()
@@ -69,7 +72,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "200", "-i", str(self.gpu)], stdout=subprocess.PIPE,
+                                          "-lms", "100", "-i", str(self.gpu)], stdout=subprocess.PIPE,
                                          stderr=subprocess.DEVNULL, text=True)
             self._t = threading.Thread(target=self._read, daemon=True)
             self._t.start()
@@ -107,19 +110,25 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
-def run_native(args) -> dict:
+def metric_name(model: str) -> str:
+    return f"train tokens/sec ({model.upper()})"
+
+
+def measure(args, K: int, W: int, with_e2e: bool = True, min_timed_s: float = 0.0) -> dict:
+    """Build one engine for ``args`` (model, mesh, kernels), time K steps device-side and (optionally) K more end to end,
+    tear everything down again.  Called collectively by every rank; returns the result dict on every rank."""
+    import gc
+    import tempfile
     import torch
     import torch.distributed as dist
-    from llmctl_b200.models.config import resolve_model
+    from llmctl_b200.comms import fused, mesh
     from llmctl_b200.ops import functional as ops
     from llmctl_b200.ops import native
     from llmctl_b200.runtime.engine import TrainingEngine, create_training_config
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
-    assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world} (launch with torchrun for N>1)"
     dp = world // (args.tp * args.pp)
     zero = args.zero_stage if args.zero_stage is not None else (1 if dp > 1 else 0)
-    import tempfile
     n_micro = args.grad_accum if args.grad_accum else (2 * args.pp if args.pp > 1 else 1)
     tc = create_training_config(
         model_name_or_path=args.model, output_dir=tempfile.mkdtemp(prefix="llmctl_bench_"),
@@ -130,9 +139,9 @@ def run_native(args) -> dict:
         kernels="baseline" if args.impl == "baseline" else "native", eval_steps=0, save_steps=0,
         logging_steps=10 ** 9, log_level="warning", metrics_jsonl=False)
     eng = TrainingEngine(tc)
-    if args.gemm:
+    if getattr(args, "gemm", None):
         ops.kernel_config().gemm = args.gemm
-    if args.attention:
+    if getattr(args, "attention", None):
         ops.kernel_config().attention = args.attention
     st = eng.state
     eng.load_model_and_tokenizer()
@@ -140,7 +149,6 @@ def run_native(args) -> dict:
     eng.setup_optimizer_and_scheduler()
     dev = st.device
     mcfg = eng.model_config
-    K, W = args.steps, args.warmup
     tokens_per_step = args.micro_batch * args.seq_len * st.dp * n_micro
 
     def barrier():
@@ -184,12 +192,32 @@ def run_native(args) -> dict:
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms_per_step = float(ms.item()) / K
+    if min_timed_s > 0 and ms_per_step * K < min_timed_s * 1e3:
+        # secondary arms only: a region this short gives the clock sampler too few samples -> time a longer one
+        K = int(min_timed_s * 1e3 / ms_per_step) + 1
+        barrier()
+        sampler = ClockSampler(st.local_rank) if st.rank == 0 else None
+        if sampler:
+            sampler.start()
+        launches0 = native.launch_count
+        ev0.record()
+        for i in range(K):
+            loss = step_resident(W + i)
+        eng.optimizer.sync_params()
+        ev1.record()
+        barrier()
+        launches = native.launch_count - launches0
+        clocks = sampler.stop() if sampler else {}
+        ms = torch.tensor([ev0.elapsed_time(ev1)], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        ms_per_step = float(ms.item()) / K
     value = tokens_per_step / (ms_per_step / 1e3)
     final_loss = float(eng._reduce_scalar(loss)) if st.pp > 1 else float(loss.detach())
 
     # ---------------- end to end through the public API: H2D every step + D2H loss read -----------------
     e2e = None
-    if not args.no_e2e:
+    if with_e2e:
         eng.train_dataloader.prefetch = False   # copy this step's inputs inside the timed region
         for _ in range(2):
             float(eng.train_step()["loss"])
@@ -216,24 +244,99 @@ def run_native(args) -> dict:
           (f"-pp{st.pp}" if st.pp > 1 else "") + ("-sp" if st.sequence_parallel else "")
     flops_tok = mcfg.flops_per_token(args.seq_len)
     kc = ops.kernel_config()
+    paths = {"gemm": kc.gemm, "attention": kc.attention, "elementwise": kc.elementwise, "optimizer": kc.optimizer}
+    rep = fused.path_report()
+    if rep is not None:          # which transport the TP all-gather GEMMs really took in this run
+        paths["k1"], paths["k1_autotune"], paths["tp_fused_calls"] = rep["k1"], rep["k1_autotune"], rep["calls"]
+    nc = getattr(eng.optimizer, "native_comm", None)
+    paths["k7"] = "fused" if nc is not None else ("nccl" if st.dp > 1 else "local")
+    if getattr(eng.optimizer, "gatherer", None) is not None:
+        paths["zero3_gather"] = "peer-memory"
     res = {
-        "metric": "train tokens/sec (GPT-7B)", "value": value, "unit": "tokens/s", "n_gpus": world, "steps": K,
+        "metric": metric_name(mcfg.name), "value": value, "unit": "tokens/s", "n_gpus": world, "steps": K,
         "warmup": W, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "bf16", "data": "synthetic tokens, random-init weights",
         "impl": args.impl,
         "config": {"model": mcfg.name, "params": mcfg.num_parameters(), "global_batch": args.micro_batch * st.dp * n_micro,
-                   "micro_batch": args.micro_batch, "seq_len": args.seq_len, "parallelism": par,
-                   "optimizer": "AdamW fp32 master + moments, clip 1.0", "activation_checkpoint": args.activation_checkpoint,
+                   "micro_batch": args.micro_batch, "micro_batches_per_step": n_micro, "seq_len": args.seq_len,
+                   "parallelism": par, "optimizer": "AdamW fp32 master + moments, clip 1.0",
+                   "activation_checkpoint": args.activation_checkpoint,
                    "l2": "inputs larger than L2: every step streams >100 GB of weights/optimizer state (L2 = 126 MB)",
-                   "kernels": {"gemm": kc.gemm, "attention": kc.attention, "elementwise": kc.elementwise,
-                               "optimizer": kc.optimizer}},
+                   "kernels": paths},
         "model_tflops_per_gpu": value * flops_tok / world / 1e12,
         "final_loss": final_loss, "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
     }
+    # ---------------- teardown: the next arm builds its own mesh ----------------
+    barrier()
+    del eng, staged, loss
+    fused.shutdown()
+    mesh.reset_state()
+    gc.collect()
+    torch.cuda.empty_cache()
+    return res
+
+
+#: BASELINE.json configurations #2-#4, measured after the headline arm of an 8-GPU run (same process group)
+EXTRA_ARMS_8 = {
+    "tp8-sp": dict(model="gpt-7b", tp=8, pp=1, sp=True, zero_stage=None, micro_batch=8, seq_len=512, grad_accum=None),
+    "dp8-zero3": dict(model="gpt-7b", tp=1, pp=1, sp=False, zero_stage=3, micro_batch=8, seq_len=512, grad_accum=None),
+    "gpt13b-tp4-pp2": dict(model="gpt-13b", tp=4, pp=2, sp=True, zero_stage=None, micro_batch=2, seq_len=2048, grad_accum=8),
+}
+
+
+def run_native(args) -> dict:
+    import copy
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world} (launch with torchrun for N>1)"
+    res = measure(args, args.steps, args.warmup, with_e2e=not args.no_e2e)
+    default_shape = (args.model == "gpt-7b" and args.tp == 1 and args.pp == 1 and args.zero_stage is None
+                     and args.impl == "native")
+    if world == 8 and default_shape and not args.no_extras:
+        # Further configurations ride on the same launch.  A watchdog makes sure the headline line is printed even
+        # if an extra arm stalls: on expiry every rank leaves, rank 0 prints what has been measured so far.
+        extras: dict = {}
+        res["other_configs"] = extras
+        t_end = time.time() + args.extras_budget_s
+
+        def bail():
+            extras["_note"] = "extras budget exhausted; remaining arms skipped"
+            if rank == 0:
+                print(json.dumps(res), flush=True)
+            os._exit(0)
+        timer = threading.Timer(args.extras_budget_s, bail)
+        timer.daemon = True
+        timer.start()
+        try:
+            for name, kw in EXTRA_ARMS_8.items():
+                if time.time() + 60 > t_end:
+                    extras[name] = {"skipped": "time budget"}
+                    continue
+                arm = copy.copy(args)
+                for k, v in kw.items():
+                    setattr(arm, k, v)
+                try:
+                    r = measure(arm, args.extra_steps, 3, with_e2e=True, min_timed_s=3.0)
+                    out = {k: r[k] for k in ("value", "ms_per_step", "steps", "clocks", "e2e", "model_tflops_per_gpu", "final_loss")}
+                    out["config"] = r["config"]
+                    extras[name] = out
+                    if kw["pp"] == 1 and time.time() + 90 < t_end:
+                        arm.impl = "baseline"            # same shape through NCCL + cuBLAS + SDPA + torch AdamW
+                        rb = measure(arm, max(args.extra_steps // 2, 4), 3, with_e2e=False)
+                        out["baseline_value"], out["baseline_ms_per_step"] = rb["value"], rb["ms_per_step"]
+                except Exception as e:  # noqa: BLE001 - an extra arm must never take the headline down
+                    extras[name] = {"error": f"{type(e).__name__}: {e}"[:300]}
+                    break                # ranks may be out of step after a failure: stop the extras here
+        finally:
+            timer.cancel()
     if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
-    return res if st.rank == 0 else None
+        try:
+            dist.barrier()
+            dist.destroy_process_group()
+        except Exception:  # noqa: BLE001
+            pass
+    return res if rank == 0 else None
 
 
 def run_reference(args) -> dict:

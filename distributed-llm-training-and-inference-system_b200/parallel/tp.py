@@ -260,12 +260,54 @@ class _VocabParallelCE(torch.autograd.Function):
         return g * dloss.to(g.dtype), None, None, None, None
 
 
+class _VocabParallelCENative(torch.autograd.Function):
+    """K15 on the TP path: the two native kernels of csrc/loss/cross_entropy.cu around two tiny all-reduces.
+    ``ce_partial`` reads the bf16 shard once (local max, sum-exp, owned target logit per row); the [rows]-sized
+    statistics are combined across the TP group (max, then sum); ``ce_finalize`` overwrites the shard in place with
+    its gradient.  No fp32 [rows, V/tp] tensor is ever materialised."""
+
+    @staticmethod
+    def forward(ctx, logits, targets, v_start, ignore_index, grad_scale):
+        from ..ops import native
+        grp, n = _tp()
+        rows, v_local = logits.shape
+        stats = torch.empty(rows, 3, dtype=torch.float32, device=logits.device)
+        native.call("llmctl_cross_entropy_partial", logits.data_ptr(), logits.stride(0), targets.data_ptr(),
+                    stats.data_ptr(), rows, v_local, int(v_start), native.stream_ptr())
+        local_max = stats[:, 0]
+        gmax = local_max.clone()
+        dist.all_reduce(gmax, op=dist.ReduceOp.MAX, group=grp)
+        packed = torch.stack([stats[:, 1] * torch.exp(local_max - gmax), stats[:, 2]])
+        dist.all_reduce(packed, group=grp)
+        lse = (gmax + packed[0].log()).contiguous()
+        valid = targets != ignore_index
+        cnt = valid.sum().clamp_min(1).float()
+        loss = (lse - packed[1]).masked_fill(~valid, 0.0).sum() / cnt * grad_scale
+        inv = (1.0 / cnt).reshape(1)
+        if logits.requires_grad:
+            native.call("llmctl_cross_entropy_finalize", logits.data_ptr(), logits.stride(0), targets.data_ptr(),
+                        lse.data_ptr(), rows, v_local, int(v_start), int(ignore_index), float(grad_scale),
+                        inv.data_ptr(), native.stream_ptr())
+        ctx.save_for_backward(logits.detach())
+        return loss
+
+    @staticmethod
+    def backward(ctx, dloss):
+        (g,) = ctx.saved_tensors      # the logits buffer now holds d(loss)/d(logits); the loss is differentiated once
+        return g, None, None, None, None
+
+
 def vocab_parallel_cross_entropy(logits: torch.Tensor, targets: torch.Tensor, ignore_index: int = -100,
                                  grad_scale: float = 1.0) -> torch.Tensor:
+    """Mean cross-entropy over logits sharded on the vocabulary.  On CUDA (native kernels) the logits buffer is
+    consumed — overwritten with its gradient — and ``.backward()`` must be called on the returned loss itself."""
     st = get_state()
     V_local = logits.shape[-1]
     logits = logits.reshape(-1, V_local)
     targets = targets.reshape(-1)
     if st.tp == 1:
         return ops.cross_entropy(logits, targets, ignore_index, grad_scale=grad_scale, assume_unit_grad=True)
+    if (ops._use_native(logits, "elementwise") and V_local % 8 == 0 and logits.stride(1) == 1
+            and logits.stride(0) % 8 == 0 and not logits.is_leaf):
+        return _VocabParallelCENative.apply(logits, targets.contiguous(), st.tp_rank * V_local, ignore_index, grad_scale)
     return _VocabParallelCE.apply(logits, targets, st.tp_rank * V_local, ignore_index, grad_scale)

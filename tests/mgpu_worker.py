@@ -375,6 +375,40 @@ def case_tp_sp_engine(out):
     out["tp_sp_engine"] = res
 
 
+def case_vocab_ce(out):
+    """K15 on the TP path: vocab-parallel cross-entropy through the native partial / finalize kernels vs fp32
+    F.cross_entropy on the full logits (loss and gradient), with ignored rows."""
+    import torch.nn.functional as F
+    from llmctl_b200.comms import mesh
+    from llmctl_b200.parallel import tp as tpl
+    world, rank = dist.get_world_size(), dist.get_rank()
+    mesh.reset_state()
+    mesh.init_mesh(tp=world)
+    torch.manual_seed(77)
+    rows, V = 1000, 4096 * world
+    full = (3.0 * torch.randn(rows, V, device="cuda")).bfloat16()
+    targets = torch.randint(0, V, (rows,), device="cuda")
+    targets[::7] = -100
+    ref_in = full.float().requires_grad_(True)
+    ref = F.cross_entropy(ref_in, targets, ignore_index=-100) * 0.5
+    ref.backward()
+    vl = V // world
+    shard = full[:, rank * vl:(rank + 1) * vl].contiguous().requires_grad_(True)
+    logits = shard * 1.0                       # non-leaf, as produced by the LM-head GEMM
+    from llmctl_b200.ops import native
+    before = native.launch_count
+    loss = tpl.vocab_parallel_cross_entropy(logits, targets, grad_scale=0.5)
+    assert native.launch_count - before == 2, "native partial/finalize kernels were not used"
+    loss.backward()
+    gref = ref_in.grad[:, rank * vl:(rank + 1) * vl]
+    e_loss = abs(float(loss) - float(ref)) / abs(float(ref))
+    e_grad = (shard.grad.float() - gref).abs().max().item() / gref.abs().max().item()
+    assert e_loss < 1e-3 and e_grad < 2e-2, (e_loss, e_grad)
+    assert shard.grad[::7].abs().max().item() == 0.0, "ignored rows must get zero gradient"
+    mesh.reset_state()
+    out["vocab_ce"] = {"loss_rel_err": e_loss, "grad_rel_err": e_grad}
+
+
 def case_watchdog(out):
     """A rank that never launches its side of a collective: the waiting kernel must give up after the deadline,
     report what it was waiting for, and the communicator must be usable again afterwards."""
@@ -468,7 +502,7 @@ def case_tp_serving(out):
     out["tp_serving"] = res
 
 
-CASES = {"tp_serving": case_tp_serving, "watchdog": case_watchdog, "probe": case_probe, "tp_kernels": case_tp_kernels, "k7_kernels": case_k7_kernels, "zero_native": case_zero_native, "zero2_native": case_zero2_native,
+CASES = {"vocab_ce": case_vocab_ce, "tp_serving": case_tp_serving, "watchdog": case_watchdog, "probe": case_probe, "tp_kernels": case_tp_kernels, "k7_kernels": case_k7_kernels, "zero_native": case_zero_native, "zero2_native": case_zero2_native,
          "zero3_native": case_zero3_native,
          "tp_sp_engine": case_tp_sp_engine}
 

@@ -44,6 +44,11 @@ def test_zero_native_matches_nccl(cuda_device):
     assert out["zero_native"]["update_rel_diff"] < 0.1 and out["zero2_native"]["update_rel_diff"] < 0.1
 
 
+def test_vocab_parallel_cross_entropy_native(cuda_device):
+    out = _run(["vocab_ce"])
+    assert out["vocab_ce"]["grad_rel_err"] < 2e-2
+
+
 def test_tp_sp_engine_fused_matches_nccl(cuda_device):
     _run(["tp_sp_engine"])
 
