@@ -387,3 +387,24 @@ int flash_bwd_v2_launch(const void* q, const void* k, const void* v, const void*
 }
 
 }  // namespace llmctl
+
+using namespace llmctl;
+
+// q,k,v,o,do: [B,S,H,128] bf16 views (token strides given in elements; do and o share o_tok_stride);
+// dq,dk,dv: outputs with token stride dqkv_tok_stride; lse: fp32 [B,H,S] from the forward;
+// scratch: fp32 [B*S*H*128 + B*H*S] (only the first 2*B*H*S floats are used: per-row log-sum-exp and delta).
+LLMCTL_API int llmctl_flash_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* d_o,
+                                     const float* lse, void* dq, void* dk, void* dv, float* scratch, int B, int S,
+                                     int H, int D, long long q_tok_stride, long long k_tok_stride,
+                                     long long v_tok_stride, long long o_tok_stride, long long dqkv_tok_stride,
+                                     float scale, int causal, void* stream) {
+  LLMCTL_BEGIN();
+  LLMCTL_REQUIRE(D == 128 && S % 128 == 0 && B > 0 && H > 0);
+  LLMCTL_REQUIRE(q_tok_stride % 8 == 0 && k_tok_stride % 8 == 0 && v_tok_stride % 8 == 0 && o_tok_stride % 8 == 0 &&
+                 dqkv_tok_stride % 8 == 0);
+  // two deterministic kernels (dK/dV, then dQ): no atomics, no fp32 dQ accumulator
+  const int rc2 = flash_bwd_v2_launch(q, k, v, o, d_o, lse, dq, dk, dv, scratch, B, S, H, q_tok_stride, k_tok_stride,
+                                      v_tok_stride, o_tok_stride, dqkv_tok_stride, scale, causal, (cudaStream_t)stream);
+  if (rc2) LLMCTL_FAIL(rc2, "flash backward");
+  return 0;
+}

@@ -32,234 +32,8 @@ constexpr int kAttnSmem = kTile /*Q*/ + 2 * kTile /*K*/ + 2 * kTile /*V*/ + kTil
 constexpr int kAttnThreads = 192;
 constexpr float kRescaleThreshold = 8.f;
 
-__global__ void __launch_bounds__(kAttnThreads, 1)
-flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
-                 const __grid_constant__ CUtensorMap tmV, __nv_bfloat16* __restrict__ O, long long o_tok_stride,
-                 float* __restrict__ lse, int S, int H, float scale_log2, float scale, int causal) {
-  extern __shared__ uint8_t smem_raw[];
-  __shared__ uint64_t bar_q, bar_kfull[2], bar_vfull[2], bar_kempty[2], bar_vempty[2];
-  __shared__ uint64_t bar_sfull[2], bar_sfree[2], bar_pready, bar_pvdone;
-  __shared__ uint32_t tmem_base_smem;
-
-  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  uint8_t* smem = smem_raw + (smem_base - smem_u32(smem_raw));
-  uint8_t* sQ = smem;
-  uint8_t* sK = smem + kTile;
-  uint8_t* sV = smem + 3 * kTile;
-  uint8_t* sP = smem + 5 * kTile;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int qblk = gridDim.x - 1 - blockIdx.x;          // heavy (late) query blocks first
-  const int head = blockIdx.y, b = blockIdx.z;
-  const int q0 = qblk * kABM;
-  const int nblk = causal ? (qblk + 1) : (S / kABN);
-  const int tok0 = b * S;
-
-  if (threadIdx.x == 0) {
-    mbar_init(&bar_q, 1);
-    for (int i = 0; i < 2; ++i) {
-      mbar_init(&bar_kfull[i], 1);
-      mbar_init(&bar_vfull[i], 1);
-      mbar_init(&bar_kempty[i], 1);
-      mbar_init(&bar_vempty[i], 1);
-      mbar_init(&bar_sfull[i], 1);
-      mbar_init(&bar_sfree[i], 4);
-    }
-    mbar_init(&bar_pready, 4);
-    mbar_init(&bar_pvdone, 1);
-    fence_mbar_init();
-  }
-  if (warp == 0 && lane == 0) {
-    prefetch_tmap(&tmQ);
-    prefetch_tmap(&tmK);
-    prefetch_tmap(&tmV);
-  }
-  if (warp == 1) tmem_alloc<1>(&tmem_base_smem, 512);
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = tmem_base_smem;
-  const uint32_t tS0 = tmem_base, tO = tmem_base + 256;   // S[0] cols 0..127, S[1] 128..255, O 256..383
-
-  if (warp == 0) {
-    if (lane == 0) {
-      mbar_expect_tx(&bar_q, kTile);
-      tma_load_3d(sQ, &tmQ, &bar_q, 0, head, tok0 + q0);
-      tma_load_3d(sQ + kPanel, &tmQ, &bar_q, 64, head, tok0 + q0);
-      for (int j = 0; j < nblk; ++j) {
-        const int st = j & 1;
-        const uint32_t ph = (j >> 1) & 1u;
-        mbar_wait(&bar_kempty[st], ph ^ 1u);
-        mbar_expect_tx(&bar_kfull[st], kTile);
-        tma_load_3d(sK + st * kTile, &tmK, &bar_kfull[st], 0, head, tok0 + j * kABN);
-        tma_load_3d(sK + st * kTile + kPanel, &tmK, &bar_kfull[st], 64, head, tok0 + j * kABN);
-        mbar_wait(&bar_vempty[st], ph ^ 1u);
-        mbar_expect_tx(&bar_vfull[st], kTile);
-        tma_load_3d(sV + st * kTile, &tmV, &bar_vfull[st], 0, head, tok0 + j * kABN);
-        tma_load_3d(sV + st * kTile + kPanel, &tmV, &bar_vfull[st], 64, head, tok0 + j * kABN);
-      }
-    }
-  } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc_qk = make_idesc_bf16(kABM, kABN, 0u, 0u);   // A, B K-major
-      constexpr uint32_t idesc_pv = make_idesc_bf16(kABM, kAD, 0u, 1u);    // A K-major (P), B MN-major (V)
-      const uint32_t q_addr = smem_base;
-      const uint32_t p_addr = smem_base + 5 * kTile;
-      auto issue_qk = [&](int j) {
-        const int st = j & 1;
-        mbar_wait(&bar_kfull[st], (j >> 1) & 1u);
-        mbar_wait(&bar_sfree[st], ((j >> 1) & 1u) ^ 1u);      // softmax finished reading S[st] of block j-2
-        tc_fence_after();
-        const uint32_t k_addr = smem_base + kTile + st * kTile;
-#pragma unroll
-        for (int ks = 0; ks < kAD / 16; ++ks) {
-          const uint32_t off = (ks >> 2) * kPanel + (ks & 3) * 32;
-          umma_ss<1>(tS0 + st * 128, make_smem_desc(q_addr + off, 16, 1024, 2),
-                     make_smem_desc(k_addr + off, 16, 1024, 2), idesc_qk, ks != 0 ? 1u : 0u);
-        }
-        umma_commit<1>(&bar_sfull[st]);
-        umma_commit<1>(&bar_kempty[st]);
-      };
-      mbar_wait(&bar_q, 0);
-      issue_qk(0);
-      for (int j = 0; j < nblk; ++j) {
-        if (j + 1 < nblk) issue_qk(j + 1);                    // overlaps the softmax of block j
-        const int st = j & 1;
-        mbar_wait(&bar_vfull[st], (j >> 1) & 1u);
-        mbar_wait(&bar_pready, j & 1u);                        // P(j) is in smem (and O was rescaled if needed)
-        tc_fence_after();
-        const uint32_t v_addr = smem_base + 3 * kTile + st * kTile;
-#pragma unroll
-        for (int ks = 0; ks < kABN / 16; ++ks) {
-          const uint64_t da = make_smem_desc(p_addr + (ks >> 2) * kPanel + (ks & 3) * 32, 16, 1024, 2);
-          const uint64_t db = make_smem_desc(v_addr + ks * 2048, kPanel, 1024, 2);
-          umma_ss<1>(tO, da, db, idesc_pv, (j | ks) != 0 ? 1u : 0u);
-        }
-        umma_commit<1>(&bar_pvdone);
-        umma_commit<1>(&bar_vempty[st]);
-      }
-    }
-  } else {
-    // ---------------------------- softmax / correction / epilogue ----------------------------
-    const int q = warp & 3;
-    const int row = q * 32 + lane;                 // query row within the tile == TMEM lane
-    const int qi = q0 + row;                       // global query index
-    const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
-    float m_ref = -INFINITY, l = 0.f;
-    for (int j = 0; j < nblk; ++j) {
-      const int st = j & 1;
-      mbar_wait(&bar_sfull[st], (j >> 1) & 1u);
-      tc_fence_after();
-      const uint32_t tS = tS0 + st * 128 + lane_off;
-      const bool diag = causal && (j == nblk - 1);
-      const int k0 = j * kABN;
-      // pass 1: block row max
-      float bm = -INFINITY;
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t r[32];
-        tmem_ld_x32(tS + c * 32, r);
-        tmem_ld_wait();
-#pragma unroll
-        for (int e = 0; e < 32; ++e) {
-          float s = __uint_as_float(r[e]) * scale_log2;
-          if (diag && (k0 + c * 32 + e > qi)) s = -INFINITY;
-          bm = fmaxf(bm, s);
-        }
-      }
-      // lazy reference update
-      float alpha = 1.f;
-      const bool need = bm > m_ref + kRescaleThreshold;
-      if (need) {
-        alpha = (m_ref == -INFINITY) ? 0.f : exp2f(m_ref - bm);
-        m_ref = bm;
-        l *= alpha;
-      }
-      // P smem and O are only free once P V of block j-1 has retired
-      if (j > 0) mbar_wait(&bar_pvdone, (j - 1) & 1u);
-      if (j > 0 && __any_sync(0xffffffffu, need)) {
-        tc_fence_after();
-#pragma unroll 1
-        for (int c = 0; c < 4; ++c) {
-          uint32_t r[32];
-          tmem_ld_x32(tO + lane_off + c * 32, r);
-          tmem_ld_wait();
-#pragma unroll
-          for (int e = 0; e < 32; ++e) r[e] = __float_as_uint(__uint_as_float(r[e]) * alpha);
-          tmem_st_x16(tO + lane_off + c * 32, r);
-          tmem_st_x16(tO + lane_off + c * 32 + 16, r + 16);
-        }
-        tmem_st_wait();
-      }
-      // pass 2: probabilities -> bf16 -> swizzled smem (K-major panels over the key index)
-      float rs = 0.f;
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t r[32];
-        tmem_ld_x32(tS + c * 32, r);
-        tmem_ld_wait();
-        uint32_t pk[16];
-#pragma unroll
-        for (int e = 0; e < 32; e += 2) {
-          float s0 = __uint_as_float(r[e]) * scale_log2, s1 = __uint_as_float(r[e + 1]) * scale_log2;
-          if (diag && (k0 + c * 32 + e > qi)) s0 = -INFINITY;
-          if (diag && (k0 + c * 32 + e + 1 > qi)) s1 = -INFINITY;
-          const float p0 = exp2f(s0 - m_ref), p1 = exp2f(s1 - m_ref);
-          rs += p0 + p1;
-          pk[e >> 1] = pack_bf16x2(p0, p1);
-        }
-        // 32 keys = 64 bytes = 4 chunks of 16 B; key index c*32 .. c*32+31 -> panel c/2, chunks (c%2)*4 .. +3
-        uint8_t* prow = sP + (c >> 1) * kPanel + row * 128;
-#pragma unroll
-        for (int ch = 0; ch < 4; ++ch) {
-          const int chunk = (c & 1) * 4 + ch;
-          *reinterpret_cast<uint4*>(prow + ((chunk ^ (row & 7)) << 4)) =
-              make_uint4(pk[ch * 4], pk[ch * 4 + 1], pk[ch * 4 + 2], pk[ch * 4 + 3]);
-        }
-      }
-      l += rs;
-      // S[st] has been fully read; P is written: publish both
-      tc_fence_before();
-      fence_proxy_async_smem();            // generic-proxy smem writes -> visible to the tensor core (async proxy)
-      __syncwarp();
-      if (lane == 0) {
-        mbar_arrive(&bar_sfree[st]);
-        mbar_arrive(&bar_pready);
-      }
-    }
-    // ---- epilogue: O / l -> bf16 -> global; LSE ----
-    mbar_wait(&bar_pvdone, (nblk - 1) & 1u);
-    tc_fence_after();
-    const float inv_l = 1.f / l;
-    __nv_bfloat16* orow = O + (static_cast<long long>(tok0 + qi)) * o_tok_stride + head * kAD;
-#pragma unroll 1
-    for (int c = 0; c < 4; ++c) {
-      uint32_t r[32];
-      tmem_ld_x32(tO + lane_off + c * 32, r);
-      tmem_ld_wait();
-#pragma unroll
-      for (int g = 0; g < 4; ++g) {
-        float f[8];
-#pragma unroll
-        for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(r[g * 8 + e]) * inv_l;
-        store8(orow + c * 32 + g * 8, pack8(f));
-      }
-    }
-    if (lse != nullptr)
-      lse[(static_cast<long long>(b) * H + head) * S + qi] = (m_ref + log2f(l)) * 0.6931471805599453f;
-    (void)scale;
-  }
-
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 1) {
-    tc_fence_after();
-    tmem_dealloc<1>(tmem_base, 512);
-  }
-}
-
-
 // =====================================================================================================
-// Version 2: one CTA = one (batch, head, 256-query block) handled as two 128-query tiles A and B that share
+// Tile structure: one work item = one (batch, head, 256-query block) handled as two 128-query tiles A and B that share
 // every K/V tile (half the K/V smem traffic) and ping-pong on the tensor core: while the softmax warpgroup of
 // tile A works on S_A, the MMA warp runs P_B V / Q_B K^T and vice versa.
 //   warps 0-3   softmax warpgroup of tile A      warps 4-7  softmax warpgroup of tile B
@@ -387,205 +161,8 @@ __device__ __forceinline__ void softmax_block_v2(uint32_t tS, uint32_t tO, int r
   tmem_st_wait();
 }
 
-__global__ void __launch_bounds__(kF2Threads, 1)
-flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
-                  const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO,
-                  float* __restrict__ lse, int S, int H, float scale_log2, int causal,
-                  long long* __restrict__ trace) {
-  extern __shared__ uint8_t smem_raw[];
-  __shared__ uint64_t bar_q[2], bar_kfull[2], bar_vfull[2], bar_kempty[2], bar_vempty[2];
-  __shared__ uint64_t bar_s[2], bar_p[2], bar_o[2];
-  __shared__ uint32_t tmem_base_smem;
-
-  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  uint8_t* smem = smem_raw + (smem_base - smem_u32(smem_raw));
-  // layout: Q_A, Q_B, K[2], V[2]
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int qb2 = gridDim.x - 1 - blockIdx.x;          // heavy (late) query blocks first
-  const int head = blockIdx.y, b = blockIdx.z;
-  const int q0 = qb2 * 2 * kABM;
-  const bool validB = q0 + kABM < S;
-  const int nblk_t0 = causal ? (2 * qb2 + 1) : (S / kABN);
-  const int nblk_t1 = validB ? (causal ? (2 * qb2 + 2) : (S / kABN)) : 0;
-  const int nblk = nblk_t1 > nblk_t0 ? nblk_t1 : nblk_t0;
-  const int tok0 = b * S;
-
-  if (threadIdx.x == 0) {
-    for (int i = 0; i < 2; ++i) {
-      mbar_init(&bar_q[i], 1);
-      mbar_init(&bar_kfull[i], 1);
-      mbar_init(&bar_vfull[i], 1);
-      mbar_init(&bar_kempty[i], 1);
-      mbar_init(&bar_vempty[i], 1);
-      mbar_init(&bar_s[i], 1);
-      mbar_init(&bar_p[i], 4);
-      mbar_init(&bar_o[i], 1);
-    }
-    fence_mbar_init();
-  }
-  if (warp == 8 && lane == 0) {
-    prefetch_tmap(&tmQ);
-    prefetch_tmap(&tmK);
-    prefetch_tmap(&tmV);
-    prefetch_tmap(&tmO);
-  }
-  if (warp == 9) tmem_alloc<1>(&tmem_base_smem, 512);
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = tmem_base_smem;
-  // optional timeline of the heaviest CTA (LLMCTL_FLASH_TRACE): trace[(role * 64 + j) * 2 + {0,1}] in SM clocks
-  const bool tracing = trace != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0;
-  const long long t_start = tracing ? clock64() : 0;
-  if (warp >= 8) {
-   setmaxnreg_dec<72>();
-   if (warp == 8) {
-    if (lane == 0) {
-      mbar_expect_tx(&bar_q[0], kTile);
-      tma_load_3d(smem, &tmQ, &bar_q[0], 0, head, tok0 + q0);
-      tma_load_3d(smem + kPanel, &tmQ, &bar_q[0], 64, head, tok0 + q0);
-      for (int j = 0; j < nblk; ++j) {
-        const int st = j & 1;
-        const uint32_t ph = (j >> 1) & 1u;
-        uint8_t* sK = smem + 2 * kTile + st * kTile;
-        uint8_t* sV = smem + 4 * kTile + st * kTile;
-        mbar_wait(&bar_kempty[st], ph ^ 1u);
-        mbar_expect_tx(&bar_kfull[st], kTile);
-        tma_load_3d(sK, &tmK, &bar_kfull[st], 0, head, tok0 + j * kABN);
-        tma_load_3d(sK + kPanel, &tmK, &bar_kfull[st], 64, head, tok0 + j * kABN);
-        if (j == 0 && validB) {        // Q_B right after the first K tile: tile A can start one load earlier
-          mbar_expect_tx(&bar_q[1], kTile);
-          tma_load_3d(smem + kTile, &tmQ, &bar_q[1], 0, head, tok0 + q0 + kABM);
-          tma_load_3d(smem + kTile + kPanel, &tmQ, &bar_q[1], 64, head, tok0 + q0 + kABM);
-        }
-        mbar_wait(&bar_vempty[st], ph ^ 1u);
-        mbar_expect_tx(&bar_vfull[st], kTile);
-        tma_load_3d(sV, &tmV, &bar_vfull[st], 0, head, tok0 + j * kABN);
-        tma_load_3d(sV + kPanel, &tmV, &bar_vfull[st], 64, head, tok0 + j * kABN);
-      }
-    }
-  } else if (warp == 9) {
-    if (lane == 0) {
-      constexpr uint32_t idesc_qk = make_idesc_bf16(kABM, kABN, 0u, 0u);   // A, B K-major
-      constexpr uint32_t idesc_pv = make_idesc_bf16(kABM, kAD, 0u, 1u);    // A from TMEM, B MN-major (V)
-      auto nblk_of = [&](int t) { return t == 0 ? nblk_t0 : nblk_t1; };
-      auto issue_qk = [&](int t, int j, bool release_k) {
-        const int st = j & 1;
-        mbar_wait(&bar_kfull[st], (j >> 1) & 1u);
-        tc_fence_after();
-        const uint32_t q_addr = smem_base + t * kTile;
-        const uint32_t k_addr = smem_base + 2 * kTile + st * kTile;
-#pragma unroll
-        for (int ks = 0; ks < kAD / 16; ++ks) {
-          const uint32_t off = (ks >> 2) * kPanel + (ks & 3) * 32;
-          umma_ss<1>(tmem_base + t * 128, make_smem_desc(q_addr + off, 16, 1024, 2),
-                     make_smem_desc(k_addr + off, 16, 1024, 2), idesc_qk, ks != 0 ? 1u : 0u);
-        }
-        umma_commit<1>(&bar_s[t]);
-        if (release_k) umma_commit<1>(&bar_kempty[st]);
-      };
-      mbar_wait(&bar_q[0], 0);
-      issue_qk(0, 0, !validB);
-      if (validB) {
-        mbar_wait(&bar_q[1], 0);
-        issue_qk(1, 0, true);
-      }
-      for (int j = 0; j < nblk; ++j) {
-        const int st = j & 1;
-        for (int t = 0; t < 2; ++t) {
-          if (j >= nblk_of(t)) continue;
-          mbar_wait(&bar_vfull[st], (j >> 1) & 1u);
-          mbar_wait(&bar_p[t], j & 1u);                      // P_t(j) is in TMEM, O_t rescaled if needed
-          tc_fence_after();
-          if (tracing && j < 64) trace[((2 + t) * 64 + j) * 2] = clock64() - t_start;
-          const uint32_t v_addr = smem_base + 4 * kTile + st * kTile;
-          const uint32_t tP = tmem_base + t * 128;
-          const uint32_t tOt = tmem_base + 256 + t * 128;
-#pragma unroll
-          for (int ks = 0; ks < kABN / 16; ++ks)
-            umma_ts<1>(tOt, tP + ks * 8, make_smem_desc(v_addr + ks * 2048, kPanel, 1024, 2), idesc_pv,
-                       (j | ks) != 0 ? 1u : 0u);
-          if (t == 1 || j >= nblk_t1) umma_commit<1>(&bar_vempty[st]);    // last reader of V(j)
-          if (j + 1 < nblk_of(t))
-            issue_qk(t, j + 1, t == 1 || j + 1 >= nblk_t1);
-          else
-            umma_commit<1>(&bar_o[t]);
-          if (tracing && j < 64) trace[((2 + t) * 64 + j) * 2 + 1] = clock64() - t_start;
-        }
-      }
-    }
-   }
-  } else {
-    setmaxnreg_inc<216>();
-    // ---------------------------- softmax warpgroups ----------------------------
-    const int t = warp >> 2;
-    const int nb = t == 0 ? nblk_t0 : nblk_t1;
-    if (nb > 0) {
-      const int q = warp & 3;                        // TMEM lane quadrant this warp may touch
-      const int row = q * 32 + lane;
-      const int qt0 = q0 + t * kABM;
-      const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
-      const uint32_t tS = tmem_base + t * 128 + lane_off;
-      const uint32_t tOt = tmem_base + 256 + t * 128 + lane_off;
-      float m_ref = -INFINITY, l0 = 0.f, l1 = 0.f;
-      for (int j = 0; j < nb; ++j) {
-        mbar_wait(&bar_s[t], j & 1u);
-        tc_fence_after();
-        if (tracing && threadIdx.x % 128 == 0 && j < 64) trace[(t * 64 + j) * 2] = clock64() - t_start;
-        if (causal && j == nb - 1)
-          softmax_block_v2<true>(tS, tOt, row, j == 0, scale_log2, m_ref, l0, l1);
-        else
-          softmax_block_v2<false>(tS, tOt, row, j == 0, scale_log2, m_ref, l0, l1);
-        tc_fence_before();
-        __syncwarp();
-        if (tracing && threadIdx.x % 128 == 0 && j < 64) trace[(t * 64 + j) * 2 + 1] = clock64() - t_start;
-        if (lane == 0) mbar_arrive(&bar_p[t]);
-      }
-      // ---- epilogue: O / l -> bf16 -> swizzled smem (the idle Q tile) -> TMA store; LSE ----
-      mbar_wait(&bar_o[t], 0);
-      tc_fence_after();
-      const float l = l0 + l1;
-      const float inv_l = 1.f / l;
-      uint8_t* stage = smem + t * kTile;
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t r[32];
-        tmem_ld_x32(tOt + c * 32, r);
-        tmem_ld_wait();
-        uint8_t* prow = stage + (c >> 1) * kPanel + row * 128;
-#pragma unroll
-        for (int ch = 0; ch < 4; ++ch) {
-          uint32_t w[4];
-#pragma unroll
-          for (int e = 0; e < 4; ++e)
-            w[e] = pack_bf16x2(__uint_as_float(r[ch * 8 + 2 * e]) * inv_l, __uint_as_float(r[ch * 8 + 2 * e + 1]) * inv_l);
-          const int chunk = (c & 1) * 4 + ch;
-          *reinterpret_cast<uint4*>(prow + ((chunk ^ (row & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
-        }
-      }
-      if (lse != nullptr)
-        lse[(static_cast<long long>(b) * H + head) * S + qt0 + row] = (m_ref + log2f(l)) * 0.6931471805599453f;
-      fence_proxy_async_smem();
-      __syncwarp();
-      if (lane == 0) {
-        tma_store_3d(&tmO, stage + q * 32 * 128, 0, head, tok0 + qt0 + q * 32);
-        tma_store_3d(&tmO, stage + kPanel + q * 32 * 128, 64, head, tok0 + qt0 + q * 32);
-        tma_store_commit();
-        tma_store_wait_read<0>();
-      }
-    }
-  }
-
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 9) {
-    tc_fence_after();
-    tmem_dealloc<1>(tmem_base, 512);
-  }
-}
-
 // =====================================================================================================
-// Version 3: version 2 made PERSISTENT.  The timeline of version 2 (tools/trace_flash.py) shows ~5.5 k clocks
+// The kernel is PERSISTENT.  The timeline of a one-CTA-per-item launch (tools/trace_flash.py) showed ~5.5 k clocks
 // between kernel start and the first usable S (barrier / TMEM set-up, tensor-map fetch, Q and K TMA latency,
 // first Q K^T) and ~3 k for the epilogue, against ~3.5 k per 256x128 iteration: at the training shape
 // (S = 512, 2-4 iterations per CTA) more than half of every CTA's life was set-up and drain, with nothing else
@@ -898,32 +475,13 @@ LLMCTL_API int llmctl_flash_attn_fwd(const void* q, const void* k, const void* v
   if (rc) LLMCTL_FAIL(rc, "tensor map K");
   rc = get_tmap_3d_bf16(&tv, v, kAD, H, rows, kAD, v_tok_stride, 64, 1, kABN, 1);
   if (rc) LLMCTL_FAIL(rc, "tensor map V");
-  static const int use_v1 = getenv("LLMCTL_FLASH_FWD_V1") ? 1 : 0;
-  static const int use_v2 = getenv("LLMCTL_FLASH_FWD_V2") ? 1 : 0;
-  if (!use_v1 && !use_v2 && scale > 0.f) {
-    // persistent kernel: one CTA per SM over a heavy-first item list
-    LLMCTL_CHECK(cudaFuncSetAttribute(flash_fwd3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kF2Smem));
-    const int n_items = ((S + 2 * kABM - 1) / (2 * kABM)) * H * B;
-    const int grid3 = n_items < kNumSMs ? n_items : kNumSMs;
-    flash_fwd3_kernel<<<grid3, kF2Threads, kF2Smem, (cudaStream_t)stream>>>(
-        tq, tk, tv, (__nv_bfloat16*)o, o_tok_stride, lse, B, S, H, scale * 1.4426950408889634f, causal,
-        flash_trace_buffer());
-    LLMCTL_RETURN_LAST();
-  }
-  if (!use_v1 && scale > 0.f) {
-    CUtensorMap to;
-    rc = get_tmap_3d_bf16(&to, o, kAD, H, rows, kAD, o_tok_stride, 64, 1, 32, 1);
-    if (rc) LLMCTL_FAIL(rc, "tensor map O");
-    LLMCTL_CHECK(cudaFuncSetAttribute(flash_fwd2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kF2Smem));
-    dim3 grid2((S + 2 * kABM - 1) / (2 * kABM), H, B);
-    flash_fwd2_kernel<<<grid2, kF2Threads, kF2Smem, (cudaStream_t)stream>>>(tq, tk, tv, to, lse, S, H,
-                                                                          scale * 1.4426950408889634f, causal,
-                                                                          flash_trace_buffer());
-    LLMCTL_RETURN_LAST();
-  }
-  LLMCTL_CHECK(cudaFuncSetAttribute(flash_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttnSmem));
-  dim3 grid(S / kABM, H, B);
-  flash_fwd_kernel<<<grid, kAttnThreads, kAttnSmem, (cudaStream_t)stream>>>(
-      tq, tk, tv, (__nv_bfloat16*)o, o_tok_stride, lse, S, H, scale * 1.4426950408889634f, scale, causal);
+  LLMCTL_REQUIRE(scale > 0.f);
+  // persistent kernel: one CTA per SM over a heavy-first item list
+  LLMCTL_CHECK(cudaFuncSetAttribute(flash_fwd3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kF2Smem));
+  const int n_items = ((S + 2 * kABM - 1) / (2 * kABM)) * H * B;
+  const int grid3 = n_items < kNumSMs ? n_items : kNumSMs;
+  flash_fwd3_kernel<<<grid3, kF2Threads, kF2Smem, (cudaStream_t)stream>>>(
+      tq, tk, tv, (__nv_bfloat16*)o, o_tok_stride, lse, B, S, H, scale * 1.4426950408889634f, causal,
+      flash_trace_buffer());
   LLMCTL_RETURN_LAST();
 }

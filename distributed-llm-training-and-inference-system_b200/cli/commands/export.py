@@ -20,7 +20,7 @@ app = typer.Typer(help="Export models to various formats")
 def convert(
     ckpt: Optional[Path] = typer.Option(None, "--ckpt", "--checkpoint", help="Checkpoint directory"),
     format: str = typer.Option("safetensors", "--format", help="safetensors | onnx | tensorrt | gguf"),
-    quant: Optional[str] = typer.Option(None, "--quant", help="int8-awq | int4-gptq"),
+    quant: Optional[str] = typer.Option(None, "--quant", help="int8 | int4 (weight-only, built in) | int8-awq | int4-gptq (declared)"),
     out: Optional[Path] = typer.Option(None, "--out", "--output", help="Output directory"),
     hf_names: bool = typer.Option(False, "--hf-names", help="Write HF LlamaForCausalLM tensor names"),
 ):

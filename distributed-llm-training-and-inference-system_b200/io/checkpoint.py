@@ -174,21 +174,25 @@ def save_checkpoint(output_dir: str | Path, step: int, model: torch.nn.Module, o
                 gc_checkpoints(output_dir, keep_latest)
 
     def finish():
+        # synchronous path (also the final save of an asynchronous multi-rank run): COMPLETE, `latest` and the GC only
+        # after every rank's shards are on disk
         write()
-        if dist.is_initialized() and not async_write:
-            dist.barrier()
-        if st.rank == 0:
-            (ckpt / "COMPLETE").write_text(str(step))
-            if not final:
-                tmp = Path(output_dir) / ".latest.tmp"
-                tmp.write_text(ckpt.name)
-                os.replace(tmp, Path(output_dir) / "latest")
-            if keep_latest:
-                gc_checkpoints(output_dir, keep_latest)
+        commit()
+
+    def finish_single_process():
+        # background thread of a one-process run: no collective may be issued from here
+        write()
+        (ckpt / "COMPLETE").write_text(str(step))
+        if not final:
+            tmp = Path(output_dir) / ".latest.tmp"
+            tmp.write_text(ckpt.name)
+            os.replace(tmp, Path(output_dir) / "latest")
+        if keep_latest:
+            gc_checkpoints(output_dir, keep_latest)
 
     global _pending_commit
     if async_write and st.world_size == 1:
-        _writer.submit(finish)
+        _writer.submit(finish_single_process)
     elif async_write and not final:
         # several ranks: each writes its own files in the background; the COMPLETE marker (which needs all of them)
         # is committed at the next synchronisation point — the next save or the end of training

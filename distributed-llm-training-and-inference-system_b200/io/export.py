@@ -6,7 +6,8 @@
   owns — used for resume after the plan changed and for loading consolidated artifacts into a TP server.
 * ``export_checkpoint`` implements ``llmctl export convert`` (reference
   llmctl/cli/commands/export.py:13-29 is a stub): ``safetensors`` (consolidated, optional HF-LLaMA key
-  names) is real; ``onnx | tensorrt | gguf`` and the quantisers fail with a clear "unsupported" error.
+  names, optional weight-only int8 / int4 quantisation) and ``gguf`` (llama.cpp container) are real; ``onnx`` and
+  ``tensorrt`` (no toolchain in the image) and the calibration-based quantisers fail with a clear "unsupported" error.
 """
 from __future__ import annotations
 
@@ -194,6 +195,10 @@ def load_pretrained_state_dict(path: str | Path) -> Dict[str, torch.Tensor]:
         raise FileNotFoundError(f"no model.safetensors (or index) under {path}")
     if any(k.startswith("model.layers.") or k.startswith("model.embed_tokens") for k in full):
         full = from_hf_llama(full)
+    meta = path / "export.json"
+    if meta.exists():
+        from .quantize import dequantize_if_needed
+        full = dequantize_if_needed(full, json.loads(meta.read_text()).get("quantization"))
     return full
 
 
@@ -201,9 +206,10 @@ def has_weights(path: str | Path) -> bool:
     p = Path(str(path))
     return p.is_dir() and ((p / "model.safetensors").exists() or (p / "model.safetensors.index.json").exists())
 
-SUPPORTED_FORMATS = ("safetensors",)
+SUPPORTED_FORMATS = ("safetensors", "gguf")
 DECLARED_FORMATS = ("safetensors", "onnx", "tensorrt", "gguf")
-DECLARED_QUANT = ("int8-awq", "int4-gptq")
+DECLARED_QUANT = ("int8-awq", "int4-gptq")      # need calibration data: declared, unsupported
+BUILTIN_QUANT = ("int8", "int4")                 # calibration-free weight-only schemes (io/quantize.py)
 
 
 def export_checkpoint(ckpt: str | Path, out: str | Path, fmt: str = "safetensors", quant: Optional[str] = None,
@@ -215,14 +221,38 @@ def export_checkpoint(ckpt: str | Path, out: str | Path, fmt: str = "safetensors
     if fmt not in SUPPORTED_FORMATS:
         raise NotImplementedError(f"export format {fmt!r} is declared by the CLI but unsupported in this build "
                                   f"(no {fmt} toolchain in the image); supported: {SUPPORTED_FORMATS}")
+    quantizer = None
     if quant:
-        raise NotImplementedError(f"quantiser {quant!r} is unsupported in this build; register one through the "
-                                  "`quantizers` plugin group (llmctl_b200.plugins.registry)")
+        from .quantize import get_quantizer
+        from ..plugins.registry import get_registry
+        quantizer = get_quantizer(quant)
+        if quantizer is None:
+            have = ", ".join(sorted(get_registry().list("quantizers"))) or "none"
+            raise NotImplementedError(f"quantiser {quant!r} is unsupported in this build (AWQ / GPTQ need a calibration "
+                                      f"set); registered weight-only quantisers: {have}")
+        if hf_names:
+            raise ValueError("--quant writes this framework's tensor layout; it cannot be combined with --hf-names")
     ckpt, out = Path(ckpt), Path(out)
     out.mkdir(parents=True, exist_ok=True)
     full = consolidate_to_state_dict(ckpt)
+    if fmt == "gguf":
+        # llama.cpp container: BF16 weights + llama.* hyper-parameters (io/gguf.py); its own k-quants are produced by
+        # llama.cpp's quantize tool from this file, so --quant does not apply here
+        if quantizer is not None or hf_names:
+            raise ValueError("--format gguf takes neither --quant nor --hf-names")
+        from .gguf import load_vocab, write_gguf
+        if not (ckpt / "model_config.json").exists():
+            raise ValueError("gguf export needs model_config.json next to the weights")
+        mc = json.loads((ckpt / "model_config.json").read_text())
+        if mc.get("norm", "rmsnorm") != "rmsnorm" or mc.get("activation", "silu") != "silu":
+            raise ValueError("gguf export writes the llama architecture: the model must use RMSNorm and a SwiGLU MLP")
+        write_gguf(out / "model.gguf", full, mc, vocab=load_vocab(ckpt))
+        (out / "export.json").write_text(json.dumps({"format": fmt, "source": str(ckpt), "tensors": len(full)}, indent=2))
+        return out
     if hf_names:
         full = to_hf_llama(full)
+    if quantizer is not None:
+        full = quantizer.quantize(full)
     save_file({k: v.contiguous() for k, v in full.items()}, str(out / "model.safetensors"), metadata={"format": "pt"})
     for f in ("model_config.json", "training_state.json"):
         if (ckpt / f).exists():
@@ -246,5 +276,5 @@ def export_checkpoint(ckpt: str | Path, out: str | Path, fmt: str = "safetensors
             hf_cfg["rope_scaling"] = {"rope_type": "linear", "factor": float(rope["factor"])}
         (out / "config.json").write_text(json.dumps(hf_cfg, indent=2))
     (out / "export.json").write_text(json.dumps({"format": fmt, "source": str(ckpt), "hf_names": hf_names,
-                                                 "tensors": len(full)}, indent=2))
+                                                 "tensors": len(full), "quantization": quant or None}, indent=2))
     return out

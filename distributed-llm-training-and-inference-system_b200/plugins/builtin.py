@@ -24,4 +24,4 @@ def register_exporters():
 
 
 def register_quantizers():
-    return {}
+    return _group("quantizers")

@@ -106,6 +106,10 @@ def _register_builtins(reg: PluginRegistry) -> None:
 
     reg.register("exporters", "safetensors", SafetensorsExporter, overwrite=True)
 
+    from ..io.quantize import BUILTIN as _QUANT
+    for name, cls in _QUANT.items():
+        reg.register("quantizers", name, cls, overwrite=True)
+
 
 _REGISTRY: Optional[PluginRegistry] = None
 

@@ -111,8 +111,15 @@ def test_train_eval_export_inspect_gc_replay(tmp_path):
     assert run("eval", "--checkpoint", str(out / "final"), "--batches", "1", "--seq-len", "32").returncode == 0   # doc spelling, short form
     r = run("export", "convert", "--ckpt", str(out / "final"), "--format", "safetensors", "--out", str(tmp_path / "art"))
     assert r.returncode == 0 and (tmp_path / "art" / "model.safetensors").exists() and (tmp_path / "art" / "model_config.json").exists()
-    r = run("export", "convert", "--ckpt", str(out / "final"), "--format", "gguf", "--out", str(tmp_path / "art2"))
+    r = run("export", "convert", "--ckpt", str(out / "final"), "--format", "onnx", "--out", str(tmp_path / "art2"))
     assert r.returncode != 0 and "unsupported" in (r.stdout + r.stderr)
+    r = run("export", "convert", "--ckpt", str(out / "final"), "--format", "gguf", "--out", str(tmp_path / "art_gguf"))
+    assert r.returncode == 0 and (tmp_path / "art_gguf" / "model.gguf").exists(), r.stdout + r.stderr
+    r = run("export", "convert", "--ckpt", str(out / "final"), "--quant", "int8", "--out", str(tmp_path / "art_q"))
+    assert r.returncode == 0 and json.loads((tmp_path / "art_q" / "export.json").read_text())["quantization"] == "int8"
+    r = run("export", "convert", "--ckpt", str(out / "final"), "--quant", "int4-gptq", "--out", str(tmp_path / "art_q2"))
+    assert r.returncode != 0 and "calibration" in (r.stdout + r.stderr)
+    assert run("serve", "start", "--artifact", str(tmp_path / "art_q"), "--dry-run").returncode == 0
     r = run("admin", "inspect", "--checkpoint", str(out / "final"), "--stats")
     assert r.returncode == 0 and "embed.weight" in r.stdout
     assert run("admin", "gc", "--output-dir", str(out), "--keep-latest", "1").returncode == 0

@@ -287,3 +287,56 @@ def test_text_dataset_is_tokenised_and_missing_sources_fail(tmp_path):
     toml.write_text('[dataset]\ntype = "tokens"\npath = "missing.bin"\n')
     with pytest.raises(FileNotFoundError):
         build_dataset(str(toml), 512, 16)
+
+
+def test_weight_only_quantizers_round_trip_and_plugin_group():
+    """int8 per-channel and int4 group-wise weight-only quantisers: registered in the `quantizers` plugin group,
+    dequantised weights stay within the expected rounding error, non-matrix tensors pass through untouched."""
+    import torch
+    from llmctl_b200.io.quantize import dequantize_if_needed, relative_error
+    from llmctl_b200.plugins.builtin import register_quantizers
+    from llmctl_b200.plugins.registry import get_registry
+    assert {"int8", "int4"} <= set(register_quantizers()) and {"int8", "int4"} <= set(get_registry().list("quantizers"))
+    torch.manual_seed(0)
+    sd = {"blocks.0.attn.qkv.weight": torch.randn(96, 256).bfloat16() * 0.05, "blocks.0.norm1.weight": torch.ones(256).bfloat16(),
+          "embed.weight": torch.randn(64, 256).bfloat16()}
+    for name, tol in (("int8", 0.01), ("int4", 0.12)):
+        q = get_registry().get("quantizers", name)()
+        packed = q.quantize(sd)
+        assert packed["blocks.0.attn.qkv.weight"].dtype in (torch.int8, torch.uint8)
+        assert packed["blocks.0.attn.qkv.weight"].numel() * packed["blocks.0.attn.qkv.weight"].element_size() <= 96 * 256
+        assert torch.equal(packed["embed.weight"], sd["embed.weight"]) and torch.equal(packed["blocks.0.norm1.weight"], sd["blocks.0.norm1.weight"])
+        back = dequantize_if_needed(packed, name)
+        assert set(back) == set(sd)
+        assert relative_error(sd["blocks.0.attn.qkv.weight"], back["blocks.0.attn.qkv.weight"]) < tol
+
+
+def test_gguf_writer_round_trip(tmp_path):
+    """GGUF v3 container: header, metadata and tensor directory parse back; q|k|v and gate|up are split, q/k rows are
+    permuted to llama.cpp's interleaved RoPE layout (an involution-free permutation checked against its definition)."""
+    import torch
+    from llmctl_b200.io.gguf import read_gguf, write_gguf
+    torch.manual_seed(1)
+    H, heads, ffn, V = 64, 4, 128, 100
+    full = {"embed.weight": torch.randn(V, H).bfloat16(), "final_norm.weight": torch.ones(H).bfloat16(),
+            "lm_head.weight": torch.randn(V, H).bfloat16(), "blocks.0.norm1.weight": torch.ones(H).bfloat16(),
+            "blocks.0.norm2.weight": torch.ones(H).bfloat16(), "blocks.0.attn.qkv.weight": torch.randn(3 * H, H).bfloat16(),
+            "blocks.0.attn.out.weight": torch.randn(H, H).bfloat16(), "blocks.0.mlp.up.weight": torch.randn(2 * ffn, H).bfloat16(),
+            "blocks.0.mlp.down.weight": torch.randn(H, ffn).bfloat16()}
+    cfg = {"name": "t", "hidden": H, "layers": 1, "ffn": ffn, "heads": heads, "vocab_size": V, "max_position_embeddings": 128}
+    meta, tensors = read_gguf(write_gguf(tmp_path / "m.gguf", full, cfg, vocab=[f"t{i}" for i in range(V)]))
+    assert meta["general.architecture"] == "llama" and meta["llama.block_count"] == 1 and meta["llama.attention.head_count"] == heads
+    assert len(meta["tokenizer.ggml.tokens"]) == V
+    assert set(tensors) == {"token_embd.weight", "output_norm.weight", "output.weight", "blk.0.attn_norm.weight", "blk.0.ffn_norm.weight",
+                            "blk.0.attn_q.weight", "blk.0.attn_k.weight", "blk.0.attn_v.weight", "blk.0.attn_output.weight",
+                            "blk.0.ffn_gate.weight", "blk.0.ffn_up.weight", "blk.0.ffn_down.weight"}
+    assert torch.equal(tensors["token_embd.weight"], full["embed.weight"]) and tensors["output_norm.weight"].dtype == torch.float32
+    q = full["blocks.0.attn.qkv.weight"][:H]
+    hd = H // heads
+    # row (head h, pair j, half s) of the rotate-half layout lands at (head h, 2j + s)
+    for h in range(heads):
+        for j in range(hd // 2):
+            assert torch.equal(tensors["blk.0.attn_q.weight"][h * hd + 2 * j], q[h * hd + j])
+            assert torch.equal(tensors["blk.0.attn_q.weight"][h * hd + 2 * j + 1], q[h * hd + hd // 2 + j])
+    assert torch.equal(tensors["blk.0.attn_v.weight"], full["blocks.0.attn.qkv.weight"][2 * H:])
+    assert torch.equal(tensors["blk.0.ffn_up.weight"], full["blocks.0.mlp.up.weight"][ffn:])
