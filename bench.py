@@ -51,6 +51,7 @@ def parse_args():
     ap.add_argument("--grad-accum", type=int, default=None, help="micro-batches per step (default 1; 2*pp with a pipeline)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="8 GPUs: skip the TP8+SP / ZeRO-3 / 13B TP4xPP2 arms")
+    ap.add_argument("--extras-selftest", action="store_true", help="2 GPUs: run scaled-down extra arms (plumbing check)")
     ap.add_argument("--extra-steps", type=int, default=20)
     ap.add_argument("--extras-budget-s", type=float, default=420.0)
     ap.add_argument("--gemm", default=None, help="override GEMM backend: native|cublas")
@@ -284,6 +285,14 @@ EXTRA_ARMS_8 = {
 }
 
 
+#: scaled-down copies of the same arms for a 2-GPU plumbing check of the extras path (--extras-selftest)
+EXTRA_ARMS_SELFTEST_2 = {
+    "tp2-sp": dict(model="gpt-1b", tp=2, pp=1, sp=True, zero_stage=None, micro_batch=4, seq_len=512, grad_accum=None),
+    "dp2-zero3": dict(model="gpt-1b", tp=1, pp=1, sp=False, zero_stage=3, micro_batch=4, seq_len=512, grad_accum=None),
+    "gpt1b-pp2": dict(model="gpt-1b", tp=1, pp=2, sp=False, zero_stage=None, micro_batch=2, seq_len=512, grad_accum=4),
+}
+
+
 def run_native(args) -> dict:
     import copy
     import torch.distributed as dist
@@ -291,9 +300,10 @@ def run_native(args) -> dict:
     rank = int(os.environ.get("RANK", "0"))
     assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world} (launch with torchrun for N>1)"
     res = measure(args, args.steps, args.warmup, with_e2e=not args.no_e2e)
-    default_shape = (args.model == "gpt-7b" and args.tp == 1 and args.pp == 1 and args.zero_stage is None
+    default_shape = (args.model in ("gpt-7b", "gpt-1b") and args.tp == 1 and args.pp == 1 and args.zero_stage is None
                      and args.impl == "native")
-    if world == 8 and default_shape and not args.no_extras:
+    arms = EXTRA_ARMS_8 if world == 8 else (EXTRA_ARMS_SELFTEST_2 if (world == 2 and args.extras_selftest) else None)
+    if arms and default_shape and not args.no_extras:
         # Further configurations ride on the same launch.  A watchdog makes sure the headline line is printed even
         # if an extra arm stalls: on expiry every rank leaves, rank 0 prints what has been measured so far.
         extras: dict = {}
@@ -309,7 +319,7 @@ def run_native(args) -> dict:
         timer.daemon = True
         timer.start()
         try:
-            for name, kw in EXTRA_ARMS_8.items():
+            for name, kw in arms.items():
                 if time.time() + 60 > t_end:
                     extras[name] = {"skipped": "time budget"}
                     continue
@@ -330,12 +340,6 @@ def run_native(args) -> dict:
                     break                # ranks may be out of step after a failure: stop the extras here
         finally:
             timer.cancel()
-    if world > 1:
-        try:
-            dist.barrier()
-            dist.destroy_process_group()
-        except Exception:  # noqa: BLE001
-            pass
     return res if rank == 0 else None
 
 
@@ -356,6 +360,24 @@ def main():
         res = run_native(args)
     if res is not None:
         print(json.dumps(res), flush=True)
+    _shutdown()
+
+
+def _shutdown():
+    """Leave the process group after the result line is out; a stuck destructor must not turn a finished run into a
+    time-out, so a timer ends the process if the orderly path takes too long."""
+    try:
+        import torch.distributed as dist
+        if not dist.is_initialized():
+            return
+        guard = threading.Timer(60.0, lambda: os._exit(0))
+        guard.daemon = True
+        guard.start()
+        dist.barrier()
+        dist.destroy_process_group()
+        guard.cancel()
+    except Exception:  # noqa: BLE001
+        pass
 
 
 if __name__ == "__main__":

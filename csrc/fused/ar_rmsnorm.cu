@@ -21,8 +21,12 @@ __global__ void __launch_bounds__(256)
 ar_residual_rmsnorm_kernel(PeerTable x, long long x_off, const void* mc_x, PeerTable pads, int slot_base,
                            int rank, int world, const __nv_bfloat16* __restrict__ residual,
                            __nv_bfloat16* __restrict__ h_out, const __nv_bfloat16* __restrict__ w,
-                           __nv_bfloat16* __restrict__ y_out, int cols, float eps, uint32_t epoch) {
+                           __nv_bfloat16* __restrict__ y_out, int cols, float eps, uint32_t epoch,
+                           const uint32_t* __restrict__ step_counter, uint32_t calls_per_step) {
   __shared__ float red[32];
+  // CUDA-graph replay: launch arguments are frozen, so the epoch is derived from a device-side step counter that a
+  // one-thread kernel bumps at the start of every decode step (epoch = call index within the step in that case)
+  if (step_counter != nullptr) epoch += *step_counter * calls_per_step;
   const int row = blockIdx.x;
   const int nvec = cols >> 3;
   // 1. publish / wait (every CTA waits; CTA 0 publishes after all local producers are done — the partial
@@ -88,18 +92,33 @@ ar_residual_rmsnorm_kernel(PeerTable x, long long x_off, const void* mc_x, PeerT
   }
 }
 
+__global__ void counter_add_kernel(uint32_t* p, uint32_t v) { *p += v; }
+
 }  // namespace llmctl
 
 using namespace llmctl;
 LLMCTL_SYMM_WATCHDOG_MODULE(ar_rmsnorm)
 
+// *counter += value on the stream (one thread): the per-step epoch source of graph-replayed peer-memory kernels.
+LLMCTL_API int llmctl_counter_add(unsigned int* counter, unsigned int value, void* stream) {
+  LLMCTL_BEGIN();
+  LLMCTL_REQUIRE(counter != nullptr);
+  counter_add_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(counter, value);
+  LLMCTL_RETURN_LAST();
+}
+
 // x: per-rank base pointers of the symmetric partial-sum buffer (bf16), x_off in elements, [rows, cols] each.
 // mc_x: NVLS multicast address of the same buffer or NULL.  slot_base: first of `world` pad slots to use.
 // residual / h_out may be NULL.  epoch: launch counter for this slot range (identical on all ranks).
+// step_counter (optional, device uint32): the effective epoch becomes *step_counter * calls_per_step + epoch, with
+// `epoch` the 1-based index of this call inside the step — the form used when the decode step is replayed as a CUDA
+// graph (llmctl_counter_add bumps the counter once per step, inside the graph).
 LLMCTL_API int llmctl_ar_residual_rmsnorm(llmctl::symm::PeerTable x, long long x_off, const void* mc_x,
                                           llmctl::symm::PeerTable pads, int slot_base, int rank, int world,
                                           const void* residual, void* h_out, const void* w, void* y_out,
-                                          int rows, int cols, float eps, unsigned int epoch, void* stream) {
+                                          int rows, int cols, float eps, unsigned int epoch,
+                                          const unsigned int* step_counter, unsigned int calls_per_step,
+                                          void* stream) {
   LLMCTL_BEGIN();
   LLMCTL_REQUIRE(world >= 1 && world <= symm::kMaxRanks && cols % 8 == 0 && cols <= 8192 && x_off % 8 == 0);
   if (rows == 0) return 0;
@@ -108,7 +127,8 @@ LLMCTL_API int llmctl_ar_residual_rmsnorm(llmctl::symm::PeerTable x, long long x
 #define LAUNCH(KV)                                                                                        \
   ar_residual_rmsnorm_kernel<KV><<<rows, 256, 0, s>>>(x, x_off, mc_x, pads, slot_base, rank, world,        \
                                                       (const __nv_bfloat16*)residual, (__nv_bfloat16*)h_out, \
-                                                      (const __nv_bfloat16*)w, (__nv_bfloat16*)y_out, cols, eps, epoch)
+                                                      (const __nv_bfloat16*)w, (__nv_bfloat16*)y_out, cols, eps, epoch, \
+                                                      step_counter, calls_per_step)
   if (kv <= 1) LAUNCH(1);
   else if (kv <= 2) LAUNCH(2);
   else LAUNCH(4);

@@ -108,13 +108,31 @@ def e2e(
     num_requests: int = typer.Option(8, "--num-requests"), max_batch_size: int = typer.Option(8, "--max-batch-size"),
     warmup_runs: int = typer.Option(1, "--warmup-runs", help="Untimed passes over the same workload first"),
     cuda_graphs: bool = typer.Option(True, "--cuda-graphs/--no-cuda-graphs"),
+    tensor_parallel: int = typer.Option(1, "--tensor-parallel", "--tp", help="TP degree (launch under torchrun with that many ranks)"),
+    kernels: str = typer.Option("native", "--kernels", help="native | baseline (cuBLAS + SDPA + ATen + NCCL all-reduce, eager)"),
     out: Optional[Path] = typer.Option(None, "--out"),
 ):
-    """Serving benchmark: p50 TTFT and decode tokens/s (BASELINE.json config #5: 2k prompt / 256 decode)."""
+    """Serving benchmark: p50 TTFT and decode tokens/s (BASELINE.json config #5: GPT-7B TP=8, 2k prompt / 256 decode:
+    ``torchrun --nproc-per-node 8 -m llmctl_b200.cli.main bench e2e --tp 8``)."""
+    import os
     import torch
+    from ...comms import mesh
+    from ...ops import functional as ops
     from ...serve.engine import InferenceEngine
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if tensor_parallel > 1:
+        if world != tensor_parallel:
+            fail(f"--tp {tensor_parallel} needs {tensor_parallel} ranks (torchrun --nproc-per-node {tensor_parallel} ...)", 2)
+        if qps is not None:
+            fail("--qps is not supported with --tp (every rank must admit the same requests in the same step)", 2)
+        mesh.reset_state()
+        mesh.init_mesh(tp=tensor_parallel)
+        torch.manual_seed(1234 + mesh.get_state().rank)
+    ops.set_backend(kernels)
+    baseline = kernels == "baseline"
     eng = InferenceEngine(model, max_batch_size=max_batch_size, max_batch_tokens=max(8192, max_batch_size * (prompt_length + gen_length)),
-                          cuda_graphs=cuda_graphs if torch.cuda.is_available() else False)
+                          cuda_graphs=(cuda_graphs and not baseline) if torch.cuda.is_available() else False,
+                          fused_tp_decode=False if baseline else None)
     V = eng.cfg.vocab_size
     g = torch.Generator().manual_seed(0)
     prompts = [torch.randint(3, min(V, 30000), (prompt_length,), generator=g).tolist() for _ in range(num_requests)]
@@ -149,11 +167,28 @@ def e2e(
            "decode_only_tokens_per_s": st["decode_tokens"] / st["decode_time_s"] if st.get("decode_time_s") else None,
            "decode_step_ms": 1e3 * st["decode_time_s"] / st["decode_steps"] if st.get("decode_steps") else None,
            "prefill_tokens_per_s": st["prefill_tokens"] / st["prefill_time_s"] if st.get("prefill_time_s") else None,
-           "cuda_graphs": bool(getattr(eng, "cuda_graphs", False)),
+           "cuda_graphs": bool(getattr(eng, "cuda_graphs", False)), "tensor_parallel": tensor_parallel, "kernels": kernels,
+           "fused_tp_allreduce": getattr(eng, "_ar", None) is not None,
            "steps": st["steps"], "preemptions": st["preemptions"]}
-    console.print_json(json.dumps(res))
-    if out:
-        Path(out).write_text(json.dumps(res, indent=2))
+    if mesh.get_state().rank == 0:
+        console.print_json(json.dumps(res))
+        if out:
+            Path(out).write_text(json.dumps(res, indent=2))
+    if tensor_parallel > 1:
+        # tear down in dependency order: graphs and symmetric buffers first, the process group last; a stuck
+        # destructor must not keep a finished benchmark alive
+        import gc
+        import threading
+        import torch.distributed as dist
+        import sys
+        sys.stdout.flush()
+        threading.Timer(30.0, lambda: os._exit(0)).start()
+        del eng
+        gc.collect()
+        torch.cuda.synchronize()
+        dist.barrier()
+        dist.destroy_process_group()
+        os._exit(0)
     return res
 
 

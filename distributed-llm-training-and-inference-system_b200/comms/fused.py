@@ -33,7 +33,9 @@ native.register_signature("llmctl_gemm_bf16_gated", [vp, vp, vp, i32, i32, i32, 
                                                      i32, i32, i32, vp])
 native.register_signature("llmctl_gemm_rs", [vp, vp, PeerTable, i32, i32, i32, i64, i64, i32, PeerTable, vp, i32, i32, u32, vp])
 native.register_signature("llmctl_rs_reduce_rmsnorm", [vp, PeerTable, i32, i32, vp, vp, vp, vp, vp, i32, i32, f32, u32, vp])
-native.register_signature("llmctl_ar_residual_rmsnorm", [PeerTable, i64, vp, PeerTable, i32, i32, i32, vp, vp, vp, vp, i32, i32, f32, u32, vp])
+native.register_signature("llmctl_ar_residual_rmsnorm", [PeerTable, i64, vp, PeerTable, i32, i32, i32, vp, vp, vp, vp, i32, i32, f32, u32,
+                                                         vp, u32, vp])
+native.register_signature("llmctl_counter_add", [vp, u32, vp])
 
 K1_FLAG_BASE = 64          # signal-pad slots [64, 64 + world * slabs) of each Xg buffer: per-slab "rows arrived" flags
 

@@ -169,9 +169,18 @@ class _DecodeAllReduce:
         from ..comms.symm import SymmBuffer
         self.rank, self.world, self.hidden, self.max_rows = st.tp_rank, st.tp, hidden, max_rows
         self.bufs = [SymmBuffer(max_rows * hidden, torch.bfloat16, st.tp_group, device) for _ in range(2)]
-        self.i, self.epoch = 0, 0
+        self.i, self.call = 0, 0
+        # Epochs come from device memory so that a decode step can be captured once and replayed: a one-thread kernel
+        # bumps `step_counter` at the start of every step, call k of the step uses epoch step * calls_per_step + k.
+        self.step_counter = torch.zeros(1, dtype=torch.int32, device=device)
+        self.calls_per_step = 0            # set by the engine: 2 per layer
         torch.cuda.synchronize(device)
         self.bufs[0].barrier()
+
+    def begin_step(self) -> None:
+        from ..ops import native
+        native.call("llmctl_counter_add", self.step_counter.data_ptr(), 1, native.stream_ptr())
+        self.i, self.call = 0, 0
 
     def partial_out(self, rows: int) -> torch.Tensor:
         return self.bufs[self.i].tensor[:rows * self.hidden].view(rows, self.hidden)
@@ -180,12 +189,14 @@ class _DecodeAllReduce:
         """all-reduce(partial in the current buffer) + residual -> h;  rmsnorm(h) * w -> y.  Returns (y, h)."""
         from ..ops import native
         buf = self.bufs[self.i]
-        self.epoch += 1
+        self.call += 1
+        assert self.call <= self.calls_per_step, "more K11 calls in a step than announced (calls_per_step)"
         h = torch.empty(rows, self.hidden, dtype=torch.bfloat16, device=buf.device)
         y = torch.empty_like(h)
         native.call("llmctl_ar_residual_rmsnorm", buf.peers, 0, buf.multicast_ptr or None, buf.pads, 16, self.rank,
                     self.world, native.ptr(residual), h.data_ptr(), norm_weight.data_ptr(), y.data_ptr(), rows,
-                    self.hidden, float(eps), self.epoch, native.stream_ptr())
+                    self.hidden, float(eps), self.call, self.step_counter.data_ptr(), self.calls_per_step,
+                    native.stream_ptr())
         self.i ^= 1
         return y, h
 
@@ -238,10 +249,11 @@ class InferenceEngine:
         self.stats = {"steps": 0, "prefill_tokens": 0, "decode_tokens": 0, "preemptions": 0, "prefill_time_s": 0.0,
                       "decode_time_s": 0.0, "decode_steps": 0}
         # decode runs as a replayed CUDA graph per (batch bucket, context bucket): the step is launch-bound
-        # (~10 small kernels per layer), so replay removes the per-kernel Python + launch cost.  TP ranks keep the
-        # eager path (the peer-signal epochs of the fused all-reduce are launch arguments, not graph-replayable).
+        # (~10 small kernels per layer), so replay removes the per-kernel Python + launch cost.
         if cuda_graphs is None:
-            cuda_graphs = self.device.type == "cuda" and self.st.tp == 1
+            # TP ranks replay the decode step too when the fused all-reduce is on (its epochs live in device memory);
+            # with NCCL all-reduces inside the step the eager path is kept
+            cuda_graphs = self.device.type == "cuda" and (self.st.tp == 1 or fused_tp_decode is not False)
         self.cuda_graphs = bool(cuda_graphs) and self.device.type == "cuda"
         # TP decode: fused all-reduce + residual + RMSNorm over peer memory (K11) instead of NCCL + two ATen kernels
         self._ar: Optional[_DecodeAllReduce] = None
@@ -253,6 +265,7 @@ class InferenceEngine:
             from ..ops import native
             if symm.available() and native.has_symbol("llmctl_ar_residual_rmsnorm") and ops.kernel_config().gemm == "native":
                 self._ar = _DecodeAllReduce(self.st, max(max_batch_size, 8), self.cfg.hidden, self.device)
+                self._ar.calls_per_step = 2 * len(self.model.blocks)
         self._graphs: Dict[Tuple[int, int], "_DecodeGraph"] = {}
         self._staging: Dict[Tuple[int, int], "_DecodeInputs"] = {}
 
@@ -356,6 +369,7 @@ class InferenceEngine:
         if self._ar is not None and B <= self._ar.max_rows:
             # fused TP path: every row-parallel partial product is reduced + normed by one K11 launch
             ar, eps = self._ar, self.cfg.layer_norm_eps
+            ar.begin_step()
             x = x.reshape(B, -1)
             y, residual = m.blocks[0].norm1(x, None)
             for i, blk in enumerate(m.blocks):
@@ -389,7 +403,8 @@ class InferenceEngine:
         B = len(seqs)
         ctx = [len(s.all_ids) for s in seqs]               # context length including the token being processed
         max_ctx = max(ctx)
-        if self.cuda_graphs:
+        use_graph = self.cuda_graphs and (self.st.tp == 1 or self._ar is not None)
+        if use_graph:
             Bb = self._bucket(B, 1, max(self.max_batch_size, 1))
             cb = self._bucket(max_ctx, 256, max(self.max_context, max_ctx))
         else:
@@ -414,7 +429,7 @@ class InferenceEngine:
             h.block_tables[r, :len(table)] = table
         inp.upload()
         self.stats["decode_tokens"] += B
-        if not self.cuda_graphs:
+        if not use_graph:
             return self._decode_core(inp, Bb, cb)[:B]
         g = self._graphs.get(key)
         if g is None:

@@ -187,7 +187,9 @@ int llmctl_adam_allgather(llmctl_peer_table params, long long bucket_off, void* 
 int llmctl_ar_residual_rmsnorm(llmctl_peer_table x, long long x_off, const void* mc_x, llmctl_peer_table pads,
                                int slot_base, int rank, int world, const void* residual, void* h_out,
                                const void* w, void* y_out, int rows, int cols, float eps, unsigned int epoch,
-                               void* stream);
+                               const unsigned int* step_counter /* optional: epoch += *step_counter * calls_per_step */,
+                               unsigned int calls_per_step, void* stream);
+int llmctl_counter_add(unsigned int* counter, unsigned int value, void* stream);
 /* watchdog: out[0] timed-out waits since the last clearing poll, out[1..6] = expected epoch, value seen,
  * blockIdx.x, flag address, ns waited, module index of the first one (out must hold 8 values). */
 int llmctl_comm_watchdog_poll(unsigned long long* out, char* module_name, int name_cap, int clear);

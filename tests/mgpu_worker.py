@@ -171,7 +171,7 @@ def case_tp_kernels(out, M=4096, K=4096, N=1536, Kl=1376):
         res_in = torch.randn(B, H, device="cuda").bfloat16()
         hout, yout = torch.empty_like(res_in), torch.empty_like(res_in)
         native.call("llmctl_ar_residual_rmsnorm", sb.peers, 0, None, sb.pads, 16, r, W, res_in.data_ptr(), hout.data_ptr(),
-                    nw.data_ptr(), yout.data_ptr(), B, H, 1e-5, it, native.stream_ptr())
+                    nw.data_ptr(), yout.data_ptr(), B, H, 1e-5, it, None, 0, native.stream_ptr())
         tot = part.float().clone(); dist.all_reduce(tot)
         hr = (tot + res_in.float())
         assert (hout.float() - hr).abs().max().item() < 0.1, "K11 h mismatch"
@@ -184,7 +184,7 @@ def case_tp_kernels(out, M=4096, K=4096, N=1536, Kl=1376):
     def k11():
         ep[0] += 1
         native.call("llmctl_ar_residual_rmsnorm", sb.peers, 0, None, sb.pads, 16, r, W, res_in.data_ptr(), hout.data_ptr(),
-                    nw.data_ptr(), yout.data_ptr(), B, H, 1e-5, ep[0], native.stream_ptr())
+                    nw.data_ptr(), yout.data_ptr(), B, H, 1e-5, ep[0], None, 0, native.stream_ptr())
 
     def base_k11():
         t = part.clone(); dist.all_reduce(t)
@@ -195,7 +195,7 @@ def case_tp_kernels(out, M=4096, K=4096, N=1536, Kl=1376):
         def k11mc():
             ep[0] += 1
             native.call("llmctl_ar_residual_rmsnorm", sb.peers, 0, sb.multicast_ptr, sb.pads, 16, r, W, res_in.data_ptr(),
-                        hout.data_ptr(), nw.data_ptr(), yout.data_ptr(), B, H, 1e-5, ep[0], native.stream_ptr())
+                        hout.data_ptr(), nw.data_ptr(), yout.data_ptr(), B, H, 1e-5, ep[0], None, 0, native.stream_ptr())
         k11mc(); torch.cuda.synchronize()
         assert (hout.float() - hr).abs().max().item() < 0.1, "K11 multimem mismatch"
         res["ar_rmsnorm_multimem_us"] = 1e3 * time_max(k11mc, iters=50)
