@@ -127,6 +127,12 @@ def measure(args, K: int, W: int, with_e2e: bool = True, min_timed_s: float = 0.
     from llmctl_b200.ops import native
     from llmctl_b200.runtime.engine import TrainingEngine, create_training_config
 
+    t_phase = {"t0": time.time()}
+
+    def mark(name):
+        now = time.time()
+        t_phase[name] = round(now - t_phase["t0"], 2)
+        t_phase["t0"] = now
     world = int(os.environ.get("WORLD_SIZE", "1"))
     dp = world // (args.tp * args.pp)
     zero = args.zero_stage if args.zero_stage is not None else (1 if dp > 1 else 0)
@@ -151,6 +157,7 @@ def measure(args, K: int, W: int, with_e2e: bool = True, min_timed_s: float = 0.
     dev = st.device
     mcfg = eng.model_config
     tokens_per_step = args.micro_batch * args.seq_len * st.dp * n_micro
+    mark("build")
 
     def barrier():
         if world > 1:
@@ -176,6 +183,7 @@ def measure(args, K: int, W: int, with_e2e: bool = True, min_timed_s: float = 0.
     for i in range(W):
         step_resident(i)
     barrier()
+    mark("warmup")
     sampler = ClockSampler(st.local_rank) if st.rank == 0 else None
     if sampler:
         sampler.start()
@@ -215,6 +223,7 @@ def measure(args, K: int, W: int, with_e2e: bool = True, min_timed_s: float = 0.
         ms_per_step = float(ms.item()) / K
     value = tokens_per_step / (ms_per_step / 1e3)
     final_loss = float(eng._reduce_scalar(loss)) if st.pp > 1 else float(loss.detach())
+    mark("timed")
 
     # ---------------- end to end through the public API: H2D every step + D2H loss read -----------------
     e2e = None
@@ -241,6 +250,7 @@ def measure(args, K: int, W: int, with_e2e: bool = True, min_timed_s: float = 0.
                "h2d_bytes_per_step": n_micro * args.micro_batch * (args.seq_len + 1) * 8,
                "d2h_bytes_per_step": 4, "api": "llmctl_b200.runtime.engine.TrainingEngine.train_step"}
 
+    mark("e2e")
     par = f"dp{st.dp}" + (f"-zero{zero}" if st.dp > 1 else "") + (f"-tp{st.tp}" if st.tp > 1 else "") + \
           (f"-pp{st.pp}" if st.pp > 1 else "") + ("-sp" if st.sequence_parallel else "")
     flops_tok = mcfg.flops_per_token(args.seq_len)
@@ -274,6 +284,9 @@ def measure(args, K: int, W: int, with_e2e: bool = True, min_timed_s: float = 0.
     mesh.reset_state()
     gc.collect()
     torch.cuda.empty_cache()
+    mark("teardown")
+    t_phase.pop("t0")
+    res["phase_s"] = t_phase
     return res
 
 
@@ -328,7 +341,7 @@ def run_native(args) -> dict:
                     setattr(arm, k, v)
                 try:
                     r = measure(arm, args.extra_steps, 3, with_e2e=True, min_timed_s=3.0)
-                    out = {k: r[k] for k in ("value", "ms_per_step", "steps", "clocks", "e2e", "model_tflops_per_gpu", "final_loss")}
+                    out = {k: r[k] for k in ("value", "ms_per_step", "steps", "clocks", "e2e", "model_tflops_per_gpu", "final_loss", "phase_s")}
                     out["config"] = r["config"]
                     extras[name] = out
                     if kw["pp"] == 1 and time.time() + 90 < t_end:
@@ -354,6 +367,9 @@ def run_reference(args) -> dict:
 
 def main():
     args = parse_args()
+    if os.environ.get("LLMCTL_BENCH_FAULTHANDLER"):
+        import faulthandler            # debugging aid: dump every thread's stack if the run is still alive after N seconds
+        faulthandler.dump_traceback_later(float(os.environ["LLMCTL_BENCH_FAULTHANDLER"]), exit=True)
     if args.impl == "reference":
         res = run_reference(args)
     else:

@@ -35,7 +35,6 @@ class ParallelState:
     dp_rank: int = 0
     tp_group: Optional[object] = None
     pp_group: Optional[object] = None
-    pp_group_up: Optional[object] = None      # second communicator over the same ranks: upstream (gradient) p2p traffic
     dp_group: Optional[object] = None
     tp_ranks: List[int] = field(default_factory=lambda: [0])
     pp_ranks: List[int] = field(default_factory=lambda: [0])
@@ -151,9 +150,8 @@ def init_mesh(tp: int = 1, pp: int = 1, dp: Optional[int] = None, sequence_paral
             for t in range(tp):
                 ranks = [p * dp * tp + d * tp + t for p in range(pp)]
                 g = dist.new_group(ranks, timeout=pg_timeout) if pp > 1 else None
-                g_up = dist.new_group(ranks, timeout=pg_timeout) if pp > 1 else None
                 if rank in ranks:
-                    st.pp_group, st.pp_group_up, st.pp_ranks = g, g_up, ranks
+                    st.pp_group, st.pp_ranks = g, ranks
     _STATE = st
     return st
 
