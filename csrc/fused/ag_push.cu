@@ -20,7 +20,7 @@
 namespace llmctl {
 using namespace symm;
 
-constexpr int kPushThreads = 512;
+constexpr int kPushThreads = 256;   // small enough to stay co-resident with a persistent GEMM CTA on the same SM
 
 __global__ void __launch_bounds__(kPushThreads)
 ag_push_kernel(const uint4* __restrict__ src, uint4* __restrict__ mc_dst, PeerTable peers, long long dst_off_vec,
@@ -28,6 +28,14 @@ ag_push_kernel(const uint4* __restrict__ src, uint4* __restrict__ mc_dst, PeerTa
                uint32_t epoch, uint32_t* __restrict__ counters, int skip_self) {
   __shared__ unsigned int s_last;
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  // P2P destinations in staggered order (rank, rank+1, ...): resolved once, kept in registers
+  uint4* dptr[kMaxRanks];
+#pragma unroll
+  for (int i = 0; i < kMaxRanks; ++i) {
+    int d = rank + i;
+    if (d >= world) d -= world;
+    dptr[i] = (i < world && !(i == 0 && skip_self)) ? reinterpret_cast<uint4*>(peers.ptr[d]) : nullptr;
+  }
   for (int sl = 0; sl < n_slabs; ++sl) {
     const uint4* s_src = src + sl * slab_vec;
     const long long base = dst_off_vec + sl * slab_vec;
@@ -44,13 +52,8 @@ ag_push_kernel(const uint4* __restrict__ src, uint4* __restrict__ mc_dst, PeerTa
     } else {
       auto put = [&](long long at, const uint4& a) {
 #pragma unroll
-        for (int i = 0; i < kMaxRanks; ++i) {
-          if (i < world) {
-            const int dst = (rank + i) % world;       // staggered: no egress hot-spot
-            if (dst == rank && skip_self) continue;
-            ptx::st_v4(reinterpret_cast<uint4*>(peers.ptr[dst]) + base + at, a);
-          }
-        }
+        for (int i = 0; i < kMaxRanks; ++i)
+          if (dptr[i] != nullptr) ptx::st_v4(dptr[i] + base + at, a);      // staggered: no egress hot-spot
       };
       for (; v + 3 * stride < slab_vec; v += 4 * stride) {
         uint4 a[4];

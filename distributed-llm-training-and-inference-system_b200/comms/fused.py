@@ -58,7 +58,7 @@ class TPFusedContext:
         self.use_multicast = os.environ.get("LLMCTL_K1_NVLS", "1") != "0"
         # the push runs on its own stream, concurrently with the GEMM's work on the rows this rank already holds
         self.push_stream = torch.cuda.Stream(device=device)
-        self.push_ctas = int(os.environ.get("LLMCTL_K1_PUSH_CTAS", "32"))
+        self.push_ctas = int(os.environ.get("LLMCTL_K1_PUSH_CTAS", "64"))
         self.tile_n = int(os.environ.get("LLMCTL_K1_TILE", "0"))            # 0 auto, 2 pair tile, 256 / 128 single-CTA tiles
         self.slab_rows = int(os.environ.get("LLMCTL_K1_SLAB_ROWS", "256"))
         self.calls = {"k1_fused": 0, "k1_nccl": 0, "k2_fused": 0}

@@ -65,3 +65,18 @@ def test_signal_watchdog_and_launch_skew(cuda_device):
 def test_tp_serving_fused_allreduce_norm(cuda_device):
     out = _run(["tp_serving"])
     assert out["tp_serving"]["first_token_agree"] == 8
+
+
+# ---- world = 8 variants (the headline TP degree / DP degree); skipped on smaller boxes ----
+def test_fused_tp_kernels_world8(cuda_device):
+    out = _run(["tp_kernels"], n=8)
+    assert out["tp_kernels"]["ag_gemm_rel_err"] < 2e-2 and out["tp_kernels"]["gemm_rs_rel_err"] < 2e-2
+
+
+def test_k7_kernels_world8(cuda_device):
+    out = _run(["k7_kernels"], n=8)
+    assert set(out["k7_kernels"]) >= {"z1_nvls", "z1_p2p", "z2", "z3"}
+
+
+def test_tp_sp_engine_world8(cuda_device):
+    _run(["tp_sp_engine", "vocab_ce"], n=8)
