@@ -64,16 +64,12 @@ class TPFusedContext:
         self.calls = {"k1_fused": 0, "k1_nccl": 0, "k2_fused": 0}
         torch.cuda.synchronize(device)
         self.xg[0].barrier()
-        # LLMCTL_K1 = fused | nccl | auto (default: time both once at start-up, all ranks agree, outcome recorded in
-        # ``k1_timing`` and reported by bench.py)
-        mode = os.environ.get("LLMCTL_K1", "auto").lower()
-        self.k1_timing = None
-        if mode == "fused" or world == 1:
-            self.use_k1 = True
-        elif mode == "nccl":
-            self.use_k1 = False
-        else:
-            self.use_k1 = self._autotune_k1()
+        # LLMCTL_K1 = fused | nccl | auto.  auto: the first time a GEMM shape is seen both paths are timed on it (all
+        # ranks agree through a MAX all-reduce) and the faster one is kept for that shape; the choices are reported by
+        # ``path_report()`` and end up in the bench line.
+        self.k1_mode = os.environ.get("LLMCTL_K1", "auto").lower()
+        self.k1_choice = {}               # (rows_local, K, N, w_mn) -> {"fused": bool, "fused_ms": .., "nccl_ms": ..}
+        self.use_k1 = self.k1_mode != "nccl"
 
     def _ag_gemm_nccl(self, x_local: torch.Tensor, w: torch.Tensor, w_mn: bool = False):
         Ms, K = x_local.shape
@@ -82,34 +78,39 @@ class TPFusedContext:
         self.calls["k1_nccl"] += 1
         return ops.gemm_raw(full, w, b_mn=w_mn), full
 
-    def _autotune_k1(self) -> bool:
-        rows = max(min(self.max_tokens // self.world, 1024) // 8 * 8, 8)
-        K = min(self.hidden, 4096)
-        N = max(min(self.hidden, 4096) // 8 * 8, 8)
-        x = torch.randn(rows, K, device=self.device).bfloat16()
-        w = torch.randn(N, K, device=self.device).bfloat16()
+    def _choose_k1(self, x_local: torch.Tensor, w: torch.Tensor, w_mn: bool) -> bool:
+        """Time both paths once on this exact shape (collective: every rank of the group gets here together)."""
+        key = (x_local.shape[0], x_local.shape[1], w.shape[1] if w_mn else w.shape[0], bool(w_mn))
+        hit = self.k1_choice.get(key)
+        if hit is not None:
+            return hit["fused"]
         times = []
-        for fn in (lambda: self._ag_gemm_fused(x, w), lambda: self._ag_gemm_nccl(x, w)):
-            for _ in range(3):
-                fn()
-            torch.cuda.synchronize(self.device)
-            dist.barrier(group=self.group)
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            for _ in range(8):
-                fn()
-            e1.record()
-            torch.cuda.synchronize(self.device)
-            times.append(e0.elapsed_time(e1) / 8)
+        with torch.no_grad():
+            for fn in (lambda: self._ag_gemm_fused(x_local, w, w_mn), lambda: self._ag_gemm_nccl(x_local, w, w_mn)):
+                for _ in range(2):
+                    fn()
+                torch.cuda.synchronize(self.device)
+                dist.barrier(group=self.group)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for _ in range(6):
+                    fn()
+                e1.record()
+                torch.cuda.synchronize(self.device)
+                times.append(e0.elapsed_time(e1) / 6)
         t = torch.tensor(times, device=self.device)
         dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
-        self.k1_timing = {"fused_ms": float(t[0]), "nccl_ms": float(t[1])}
-        self.calls = {k: 0 for k in self.calls}
-        return bool(t[0] <= 1.02 * t[1])
+        self.calls["k1_fused"] -= 8
+        self.calls["k1_nccl"] -= 8
+        self.k1_choice[key] = {"fused": bool(t[0] <= t[1]), "fused_ms": round(float(t[0]), 4), "nccl_ms": round(float(t[1]), 4)}
+        return self.k1_choice[key]["fused"]
 
     def path_report(self) -> dict:
         """Which transport the all-gather GEMMs took (for bench lines and logs)."""
-        return {"k1": "fused" if self.use_k1 else "nccl", "k1_autotune": self.k1_timing, "calls": dict(self.calls)}
+        picks = {"x".join(map(str, k[:3])) + ("t" if k[3] else ""): v for k, v in self.k1_choice.items()}
+        n_f = sum(1 for v in self.k1_choice.values() if v["fused"])
+        k1 = self.k1_mode if self.k1_mode in ("fused", "nccl") else f"auto ({n_f} of {len(self.k1_choice)} shapes fused)"
+        return {"k1": k1, "k1_autotune": picks or None, "calls": dict(self.calls)}
 
     # per-op gates on the real buffer requirement (the row-parallel input already has all M rows)
     def usable_ag(self, x: torch.Tensor) -> bool:
@@ -129,12 +130,12 @@ class TPFusedContext:
         return buf, full, full[self.rank * rows_local:(self.rank + 1) * rows_local]
 
     def ag_gemm(self, x_local: torch.Tensor, w: torch.Tensor, w_mn: bool = False):
-        """x_local [Ms, K] -> (y [M, N], Xg [M, K]).  ``w`` is [N, K], or [K, N] with ``w_mn`` (a row-parallel forward
-        weight used untransposed for its dgrad).  Fused push + gated GEMM, or NCCL all-gather + GEMM where the start-up
-        measurement found that faster (see ``use_k1``)."""
-        if not self.use_k1:
-            return self._ag_gemm_nccl(x_local, w, w_mn)
-        return self._ag_gemm_fused(x_local, w, w_mn)
+        """x_local [Ms, K] -> (y [M, N], Xg [M, K], xg_is_symmetric).  ``w`` is [N, K], or [K, N] with ``w_mn`` (a
+        row-parallel forward weight used untransposed for its dgrad).  Fused push + gated GEMM, or NCCL all-gather + GEMM
+        where the per-shape measurement found that faster."""
+        if self.k1_mode != "nccl" and (self.k1_mode == "fused" or self._choose_k1(x_local, w, w_mn)):
+            return (*self._ag_gemm_fused(x_local, w, w_mn), True)       # Xg is a view of the recycled symmetric buffer
+        return (*self._ag_gemm_nccl(x_local, w, w_mn), False)
 
     def _ag_gemm_fused(self, x_local: torch.Tensor, w: torch.Tensor, w_mn: bool = False):
         Ms, K = x_local.shape
@@ -188,8 +189,8 @@ class _AGLinearFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x_local, w):
-        y, xg_full = _ctx.ag_gemm(x_local, w)
-        ctx.save_for_backward(xg_full.clone() if (_ctx.world > 1 and _ctx.use_k1) else xg_full, w)   # the symmetric Xg is recycled two calls later
+        y, xg_full, recycled = _ctx.ag_gemm(x_local, w)
+        ctx.save_for_backward(xg_full.clone() if recycled else xg_full, w)   # the symmetric Xg is recycled two calls later
         return y
 
     @staticmethod
@@ -223,7 +224,7 @@ class _LinearRSFn(torch.autograd.Function):
     def backward(ctx, dh):
         x, w = ctx.saved_tensors
         dh = dh if dh.is_contiguous() else dh.contiguous()
-        dx, dh_full = _ctx.ag_gemm(dh, w, w_mn=True)        # dX = all_gather(dh) @ w, w [N, K_local] read MN-major
+        dx, dh_full, _ = _ctx.ag_gemm(dh, w, w_mn=True)     # dX = all_gather(dh) @ w, w [N, K_local] read MN-major
         mg = getattr(w, "main_grad", None)
         if mg is not None:
             fresh = getattr(w, "_main_grad_fresh", False)

@@ -2,7 +2,8 @@
 
 ``attention(q, k, v)`` takes ``[B, S, H, D]`` views (typically slices of the packed qkv activation) and
 dispatches to the tcgen05 flash-attention kernels (``csrc/attention``) when they are built and the shape is
-supported (bf16, D=128 or 64, S multiple of 128), else to PyTorch SDPA (baseline path).
+supported (bf16, head_dim 128; causal sequences of any length — ragged ones are padded to the 128-token tile), else to
+PyTorch SDPA (head_dim 64 models such as gpt-125m, non-causal ragged shapes, CPU).
 
 Reference: the reference never calls attention itself — HF modules pick SDPA/eager behind
 ``self.model(**batch)`` (reference llmctl/runtime/engine.py:284); its tuner benchmarks a naive
@@ -94,6 +95,16 @@ def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, causal: bool = 
     scale = scale if scale is not None else 1.0 / math.sqrt(q.shape[-1])
     if _native_ok(q, k, v):
         return _FlashAttnFn.apply(q, k, v, scale, causal)
+    S = q.shape[1]
+    if (causal and S % 128 and q.is_cuda and q.dtype == torch.bfloat16 and q.shape[-1] == 128
+            and kernel_config().attention == "native" and native.has_symbol("llmctl_flash_attn_fwd")):
+        # ragged length (every serving prefill): pad the sequence to the kernel's 128-token tile.  Under the causal
+        # mask the zero keys appended at the end are invisible to every real query; the padded queries' rows are
+        # dropped.  (Differentiable: F.pad / slicing carry the gradient.)
+        pad = 128 - S % 128
+        qp, kp, vp = (F.pad(t, (0, 0, 0, 0, 0, pad)) for t in (q, k, v))
+        if _native_ok(qp, kp, vp):
+            return _FlashAttnFn.apply(qp, kp, vp, scale, causal)[:, :S]
     return _sdpa(q, k, v, causal, scale)
 
 

@@ -182,9 +182,26 @@ class CommunicationTuner(Tunable):
         self.link_gbps, self.latency_us = link_gbps, latency_us
         self.measured = False
 
+    def _native_available(self) -> bool:
+        try:
+            import torch.distributed as dist
+            from ..comms import symm
+            from ..ops import native
+            return (dist.is_initialized() and dist.get_world_size() > 1 and symm.available()
+                    and native.has_symbol("llmctl_allreduce_multimem"))
+        except Exception:  # noqa: BLE001
+            return False
+
     def get_parameter_space(self):
-        return {"bucket_size_mb": [25, 50, 100, 200, 400], "overlap_computation": [True, False],
-                "compression": ["none", "bf16"]}
+        space = {"bucket_size_mb": [25, 50, 100, 200, 400], "overlap_computation": [True, False],
+                 "compression": ["none", "bf16"]}
+        # under torchrun on GPUs the peer-memory collectives of this framework are a tunable transport next to NCCL:
+        # in-switch (NVLS multimem) all-reduce for large buckets, one-shot P2P pull for small ones, with the number of
+        # CTAs given to the collective as a second knob (it shares the SMs with backward)
+        if self._native_available():
+            space["transport"] = ["nccl", "native"]
+            space["comm_ctas"] = [0, 32]
+        return space
 
     def validate_parameters(self, p):
         return p["bucket_size_mb"] > 0
@@ -206,6 +223,21 @@ class CommunicationTuner(Tunable):
             flat = t.reshape(-1)
             per = math.ceil(flat.numel() / n_buckets)
             chunks = [flat[i * per:(i + 1) * per] for i in range(n_buckets)]
+            if p.get("transport") == "native":
+                if flat.dtype != torch.bfloat16:
+                    raise ValueError("the peer-memory all-reduce works on bf16 buckets (use compression=bf16)")
+                from ..comms.collectives import PeerCollectives
+                per8 = (per + 7) // 8 * 8
+                pc = getattr(self, "_pc", None)
+                if pc is None or pc.buf.tensor.numel() < per8:
+                    pc = self._pc = PeerCollectives(per8)
+                ctas = int(p.get("comm_ctas", 0))
+
+                def fn_native():
+                    for c in chunks:
+                        pc.buf.tensor[:c.numel()].copy_(c)
+                        pc.all_reduce((c.numel() + 7) // 8 * 8, max_ctas=ctas)
+                return _time_call(fn_native, "cuda", self.cfg.warmup_iterations, self.cfg.measurement_iterations)
 
             def fn():
                 works = [dist.all_reduce(c, async_op=True) for c in chunks]

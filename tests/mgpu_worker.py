@@ -119,7 +119,8 @@ def case_tp_kernels(out, M=4096, K=4096, N=1536, Kl=1376):
             sweep[f"tile{tile}_slab{slab}"] = time_max(lambda: ctx._ag_gemm_fused(x_local, w), iters=20)
     ctx.tile_n, ctx.slab_rows = 0, 256
     res["ag_gemm_ms_sweep"] = sweep
-    res["k1_autotune"] = {"use_k1": ctx.use_k1, "timing": ctx.k1_timing}
+    ctx.ag_gemm(x_local, w)                    # auto mode: times both paths on this shape once
+    res["k1_autotune"] = ctx.path_report()
     # MN-major weight (backward of a row-parallel layer): same product from w^T stored [K, N]
     wt = w.t().contiguous()
     y_mn, _ = ctx._ag_gemm_fused(x_local, wt, w_mn=True)
@@ -296,11 +297,11 @@ def case_k7_kernels(out):
     out["k7_kernels"] = res
 
 
-def _zero_traj(stage, comm, steps=4):
+def _zero_traj(stage, comm, steps=4, tp=1):
     from llmctl_b200.comms import mesh
     from llmctl_b200.parallel.zero import ZeroOptimizer
     from llmctl_b200.runtime.engine import LRSchedule
-    eng = _engine(dict(zero_stage=stage))
+    eng = _engine(dict(zero_stage=stage, tensor_parallel=tp, sequence_parallel=tp > 1))
     c = eng.config
     eng.optimizer = ZeroOptimizer(eng.model, lr=c.learning_rate, betas=tuple(c.betas), eps=c.adam_eps, weight_decay=c.weight_decay,
                                   zero_stage=stage, grad_clip=c.gradient_clipping, state=eng.state, comm=comm)
@@ -315,13 +316,15 @@ def _zero_traj(stage, comm, steps=4):
         p_end = torch.cat([p.detach().float().reshape(-1) for p in eng.model.parameters()])
     info = {"native": eng.optimizer.native_comm is not None, "gatherer": eng.optimizer.gatherer is not None}
     torch.cuda.synchronize(); dist.barrier()
+    from llmctl_b200.comms import fused
+    fused.shutdown()
     mesh.reset_state()
     return losses, p_end - p_init, info
 
 
-def _compare_zero(out, key, stage):
-    ref_l, ref_d, _ = _zero_traj(stage, "nccl")
-    nat_l, nat_d, info = _zero_traj(stage, "native")
+def _compare_zero(out, key, stage, tp=1):
+    ref_l, ref_d, _ = _zero_traj(stage, "nccl", tp=tp)
+    nat_l, nat_d, info = _zero_traj(stage, "native", tp=tp)
     assert info["native"], "K7 path was not enabled"
     if stage >= 3:
         assert info["gatherer"], "peer gatherer was not enabled"
@@ -341,6 +344,14 @@ def case_zero_native(out):
 
 def case_zero2_native(out):
     _compare_zero(out, "zero2_native", 2)
+
+
+def case_zero_tp_native(out):
+    """K7 on a DP x TP mesh (tp = 2 with sequence parallelism, dp = world / 2): the DP group is a sub-group, the
+    gradient norm also needs the TP ranks' contributions (handed to the kernel as a device scalar)."""
+    assert dist.get_world_size() >= 4 and dist.get_world_size() % 2 == 0, "needs >= 4 GPUs"
+    _compare_zero(out, "zero1_tp2_native", 1, tp=2)
+    _compare_zero(out, "zero3_tp2_native", 3, tp=2)
 
 
 def case_zero3_native(out):
@@ -502,7 +513,7 @@ def case_tp_serving(out):
     out["tp_serving"] = res
 
 
-CASES = {"vocab_ce": case_vocab_ce, "tp_serving": case_tp_serving, "watchdog": case_watchdog, "probe": case_probe, "tp_kernels": case_tp_kernels, "k7_kernels": case_k7_kernels, "zero_native": case_zero_native, "zero2_native": case_zero2_native,
+CASES = {"vocab_ce": case_vocab_ce, "tp_serving": case_tp_serving, "watchdog": case_watchdog, "probe": case_probe, "tp_kernels": case_tp_kernels, "k7_kernels": case_k7_kernels, "zero_native": case_zero_native, "zero2_native": case_zero2_native, "zero_tp_native": case_zero_tp_native,
          "zero3_native": case_zero3_native,
          "tp_sp_engine": case_tp_sp_engine}
 

@@ -80,3 +80,8 @@ def test_k7_kernels_world8(cuda_device):
 
 def test_tp_sp_engine_world8(cuda_device):
     _run(["tp_sp_engine", "vocab_ce"], n=8)
+
+
+def test_k7_on_dp_x_tp_mesh(cuda_device):
+    out = _run(["zero_tp_native"], n=4)
+    assert out["zero1_tp2_native"]["update_rel_diff"] < 0.1 and out["zero3_tp2_native"]["update_rel_diff"] < 0.1
