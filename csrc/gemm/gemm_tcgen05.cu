@@ -62,12 +62,12 @@ constexpr int kGemmThreads = 192;
 
 template <int BN>
 struct GemmCfg {
-  static constexpr int kStages = (BN == 256) ? 4 : 6;
+  static constexpr int kStages = (BN == 256) ? 4 : (BN == 192 ? 5 : 6);
   static constexpr int kABytes = kBM * kBK * 2;
   static constexpr int kBBytes = BN * kBK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kSmemBytes = kStages * kStageBytes + 1024;  // + alignment slack
-  static constexpr int kTmemCols = 2 * BN;
+  static constexpr int kTmemCols = (2 * BN <= 256) ? 256 : 512;   // power of two >= 2 accumulators of BN columns
 };
 
 // Epilogue modes
@@ -292,21 +292,24 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 //   tfull[a]  (both CTAs)  : tcgen05.commit multicast from the leader
 //   tempty[a] (leader only): 8 arrives = 4 epilogue warps x 2 CTAs (peer arrives remotely)
 // ================================================================================================
+// PBN = N of the pair tile: 256 (the throughput tile) or 128 (half the work per tile: fills the last wave of the
+// 1-3 wave problems of a TP=8 shard, where a 256 x 256 tile is 26 us of tensor-core time).
+template <int PBN>
 struct Gemm2Cfg {
-  static constexpr int kBN = 256;            // N of the pair tile
-  static constexpr int kStages = 6;
+  static constexpr int kBN = PBN;
+  static constexpr int kStages = (PBN == 256) ? 6 : 8;
   static constexpr int kABytes = kBM * kBK * 2;          // 128 x 64 per CTA
-  static constexpr int kBBytes = (kBN / 2) * kBK * 2;    // 128 x 64 per CTA
-  static constexpr int kStageBytes = kABytes + kBBytes;  // 32 KB per CTA
+  static constexpr int kBBytes = (kBN / 2) * kBK * 2;    // (PBN/2) x 64 per CTA
+  static constexpr int kStageBytes = kABytes + kBBytes;  // 32 / 24 KB per CTA
   static constexpr int kSmemBytes = kStages * kStageBytes + 1024;
-  static constexpr int kTmemCols = 512;
+  static constexpr int kTmemCols = 2 * PBN;              // 512 / 256
 };
 
-template <bool A_MN, bool B_MN, typename OutT>
+template <int PBN, bool A_MN, bool B_MN, typename OutT>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
 gemm2_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                      OutT* __restrict__ C, long long ldc, int M, int N, int K, int beta, const GemmGate gate) {
-  using Cfg = Gemm2Cfg;
+  using Cfg = Gemm2Cfg<PBN>;
   constexpr int BN = Cfg::kBN;
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t bar_full[Cfg::kStages];
@@ -554,7 +557,7 @@ static int dispatch_layout(int a_mn, int b_mn, const void* A, const void* B, voi
 }
 
 
-template <bool A_MN, bool B_MN, typename OutT>
+template <int PBN, bool A_MN, bool B_MN, typename OutT>
 static int launch_gemm2(const void* A, const void* B, void* C, int M, int N, int K, long long lda,
                         long long ldb, long long ldc, int beta, int max_ctas, cudaStream_t s, GemmGate gate) {
   if (gate.flags) {
@@ -563,7 +566,7 @@ static int launch_gemm2(const void* A, const void* B, void* C, int M, int N, int
     gate.perm = (gate.perm && (M / gate.world) % (2 * kBM) == 0 && gate.rows_per_flag % (2 * kBM) == 0 &&
                  M % gate.world == 0) ? 1 : 0;
   }
-  using Cfg = Gemm2Cfg;
+  using Cfg = Gemm2Cfg<PBN>;
   CUtensorMap tmA, tmB;
   int rc;
   if (!A_MN) rc = get_tmap_2d_bf16(&tmA, A, M, K, lda, kBM, kBK, 1);
@@ -572,7 +575,7 @@ static int launch_gemm2(const void* A, const void* B, void* C, int M, int N, int
   if (!B_MN) rc = get_tmap_2d_bf16(&tmB, B, N, K, ldb, Cfg::kBN / 2, kBK, 1);
   else rc = get_tmap_2d_bf16(&tmB, B, K, N, ldb, kBK, 64, 1);
   if (rc) LLMCTL_FAIL(rc, "tensor map B");
-  auto kern = gemm2_tcgen05_kernel<A_MN, B_MN, OutT>;
+  auto kern = gemm2_tcgen05_kernel<PBN, A_MN, B_MN, OutT>;
   LLMCTL_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     Cfg::kSmemBytes));
   const int tiles = ((M + 2 * kBM - 1) / (2 * kBM)) * ((N + Cfg::kBN - 1) / Cfg::kBN);
@@ -584,14 +587,14 @@ static int launch_gemm2(const void* A, const void* B, void* C, int M, int N, int
   LLMCTL_RETURN_LAST();
 }
 
-template <typename OutT>
+template <int PBN, typename OutT>
 static int dispatch_layout2(int a_mn, int b_mn, const void* A, const void* B, void* C, int M, int N,
                             int K, long long lda, long long ldb, long long ldc, int beta,
                             int max_ctas, cudaStream_t s, const GemmGate& g) {
-  if (!a_mn && !b_mn) return launch_gemm2<false, false, OutT>(A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s, g);
-  if (!a_mn && b_mn) return launch_gemm2<false, true, OutT>(A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s, g);
-  if (a_mn && !b_mn) return launch_gemm2<true, false, OutT>(A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s, g);
-  return launch_gemm2<true, true, OutT>(A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s, g);
+  if (!a_mn && !b_mn) return launch_gemm2<PBN, false, false, OutT>(A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s, g);
+  if (!a_mn && b_mn) return launch_gemm2<PBN, false, true, OutT>(A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s, g);
+  if (a_mn && !b_mn) return launch_gemm2<PBN, true, false, OutT>(A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s, g);
+  return launch_gemm2<PBN, true, true, OutT>(A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s, g);
 }
 
 }  // namespace llmctl
@@ -599,7 +602,7 @@ static int dispatch_layout2(int a_mn, int b_mn, const void* A, const void* B, vo
 using namespace llmctl;
 
 // D[M,N] = op(A) op(B) (+ D if beta).  a_mn / b_mn select the operand storage (see file header).
-// out_fp32: D is fp32 (else bf16).  tile_n: 0 = auto, 128 or 256 (1-CTA tiles), 2 = 256x256 CTA-pair tile.  max_ctas: 0 = all SMs
+// out_fp32: D is fp32 (else bf16).  tile_n: 0 = auto, 128 / 192 / 256 (1-CTA tiles), 2 = 256x256 CTA-pair tile, 3 = 256x128 CTA-pair tile.  max_ctas: 0 = all SMs
 // (a smaller value leaves SMs free for a concurrent communication kernel).
 static int gemm_bf16_impl(const void* A, const void* B, void* C, int M, int N, int K,
                           long long lda, long long ldb, long long ldc, int a_mn, int b_mn,
@@ -613,19 +616,33 @@ static int gemm_bf16_impl(const void* A, const void* B, void* C, int M, int N, i
   cudaStream_t s = (cudaStream_t)stream;
   // auto: the CTA-pair kernel wins whenever the problem has at least one full pair tile in each dimension
   // (measured on B200: 1.44-1.61 PFLOP/s vs 1.24-1.45 for the single-CTA 128x256 tile on the GPT-7B shapes)
+  // auto: the 256 x 256 CTA-pair tile wins whenever the problem has at least one full pair tile in each dimension
+  // (measured on B200: 1.44-1.61 PFLOP/s vs 1.24-1.45 for the single-CTA 128x256 tile on the GPT-7B shapes).  The
+  // narrower tiles (192, pair 256 x 128) were added for the 1-3 wave problems of a TP=8 shard and measured SLOWER
+  // there too (4096 x 1536 x 4096: 55 us pair-256, 53 us 192, 85 us pair-128, cuBLAS 42 us): the main loop costs about
+  // the same per 64-deep k-block whatever the tile width (operand traffic from L2, not the tensor pipe, sets the pace),
+  // so less work per tile only lowers the rate.  They stay selectable (tile_n = 192 / 3), never chosen automatically.
   if (tile_n == 0 && M > 128 && N > 128) tile_n = 2;
   if (tile_n == 2) {   // 2-CTA pair tile 256 x 256 (cta_group::2)
-    if (out_fp32) return dispatch_layout2<float>(a_mn, b_mn, A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s, g);
-    return dispatch_layout2<__nv_bfloat16>(a_mn, b_mn, A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s, g);
+    if (out_fp32) return dispatch_layout2<256, float>(a_mn, b_mn, A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s, g);
+    return dispatch_layout2<256, __nv_bfloat16>(a_mn, b_mn, A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s, g);
+  }
+  if (tile_n == 3) {   // 2-CTA pair tile 256 x 128
+    if (out_fp32) return dispatch_layout2<128, float>(a_mn, b_mn, A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s, g);
+    return dispatch_layout2<128, __nv_bfloat16>(a_mn, b_mn, A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s, g);
   }
   int bn = tile_n;
-  if (bn != 128 && bn != 256) {
+  if (bn != 128 && bn != 192 && bn != 256) {
     const int sms = num_sms();
     const long long t256 = static_cast<long long>((M + 127) / 128) * ((N + 255) / 256);
     const long long t128 = static_cast<long long>((M + 127) / 128) * ((N + 127) / 128);
     const double c256 = static_cast<double>((t256 + sms - 1) / sms) * 2.0;
     const double c128 = static_cast<double>((t128 + sms - 1) / sms) * 1.45;  // measured: a 128-wide tile runs at ~0.7x the rate
     bn = (c128 < c256) ? 128 : 256;
+  }
+  if (bn == 192) {
+    if (out_fp32) return dispatch_layout<192, float>(a_mn, b_mn, A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s, g);
+    return dispatch_layout<192, __nv_bfloat16>(a_mn, b_mn, A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s, g);
   }
   if (bn == 256) {
     if (out_fp32) return dispatch_layout<256, float>(a_mn, b_mn, A, B, C, M, N, K, lda, ldb, ldc, beta, max_ctas, s, g);

@@ -195,6 +195,9 @@ class TrainingEngine:
         ops.set_backend(c.kernels)
         if c.deterministic:
             torch.use_deterministic_algorithms(True, warn_only=True)
+            # K7: gradients are summed by rank-ordered fp32 P2P pulls instead of the in-switch reduction, whose
+            # summation order is not specified (the NVLS parameter push is a plain copy and stays on)
+            os.environ.setdefault("LLMCTL_K7_NVLS_REDUCE", "0")
             torch.backends.cudnn.benchmark = False
         if self.is_main:
             self.logger.info("mesh: world=%d tp=%d pp=%d dp=%d sp=%s zero=%d backend=%s device=%s",

@@ -200,6 +200,17 @@ def case_tp_kernels(out, M=4096, K=4096, N=1536, Kl=1376):
         k11mc(); torch.cuda.synchronize()
         assert (hout.float() - hr).abs().max().item() < 0.1, "K11 multimem mismatch"
         res["ar_rmsnorm_multimem_us"] = 1e3 * time_max(k11mc, iters=50)
+    # roofline fractions of the fused paths: the slower of compute at the measured bf16 peak and NVLink bytes at the
+    # measured link rate, over the achieved time (BASELINE.json north star, metrics/roofline.py)
+    from llmctl_b200.metrics.roofline import RooflinePoint
+    res["roofline"] = {
+        "k1_ag_gemm": RooflinePoint("ag_gemm", res["ag_gemm_ms"] * 1e-3, flops=2.0 * M * N * K,
+                                    nvlink_bytes=(W - 1) * Ms * K * 2).report(),
+        "k2_gemm_rs": RooflinePoint("gemm_rs+reduce+norm", res["gemm_rs_norm_ms"] * 1e-3, flops=2.0 * M * 4096 * Kl,
+                                    nvlink_bytes=(W - 1) * Ms * 4096 * 2).report(),
+        "k11_ar_rmsnorm": RooflinePoint("ar_residual_rmsnorm", res["ar_rmsnorm_us"] * 1e-6,
+                                        nvlink_bytes=(W - 1) * B * H * 2).report(),
+    }
     out["tp_kernels"] = res
     fused.shutdown()
 

@@ -166,7 +166,7 @@ def test_gemm_layouts(cuda_device, M, N, K, a_mn, b_mn):
     ref = A.float() @ B.float().t()
     a_arg = A.t().contiguous() if a_mn else A
     b_arg = B.t().contiguous() if b_mn else B
-    for tile_n in (128, 256, 2):
+    for tile_n in (128, 192, 256, 2, 3, 0):
         out = ops.gemm_raw(a_arg, b_arg, a_mn=a_mn, b_mn=b_mn, tile_n=tile_n)
         _close(out, ref, 0.05 * math.sqrt(K / 64), 2e-2, f"gemm tile_n={tile_n}")
 
