@@ -262,7 +262,10 @@ def measure(args, K: int, W: int, with_e2e: bool = True, min_timed_s: float = 0.
     nc = getattr(eng.optimizer, "native_comm", None)
     paths["k7"] = "fused" if nc is not None else ("nccl" if st.dp > 1 else "local")
     if getattr(eng.optimizer, "gatherer", None) is not None:
-        paths["zero3_gather"] = "peer-memory"
+        g = eng.optimizer.gatherer
+        paths["zero3_gather"] = "peer-memory push" + (", first GEMM of a block consumes it through arrival flags (K8)"
+                                                      if g.gate_first_gemm else "")
+        paths["k8_calls"] = dict(g.stats)
     res = {
         "metric": metric_name(mcfg.name), "value": value, "unit": "tokens/s", "n_gpus": world, "steps": K,
         "warmup": W, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",

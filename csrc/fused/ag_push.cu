@@ -73,7 +73,8 @@ ag_push_kernel(const uint4* __restrict__ src, uint4* __restrict__ mc_dst, PeerTa
       if (s_last) atomicExch(&counters[sl], 0u);
     }
     __syncthreads();
-    if (s_last && threadIdx.x < world && static_cast<int>(threadIdx.x) != rank)
+    // (the local copy needs a flag too when this kernel wrote it, i.e. when the source was not already in place)
+    if (s_last && threadIdx.x < world && (static_cast<int>(threadIdx.x) != rank || !skip_self))
       signal_set(reinterpret_cast<uint32_t*>(pads.ptr[threadIdx.x]) + flag_base + first_flag + sl, epoch);
     __syncthreads();
   }
@@ -108,6 +109,24 @@ LLMCTL_API int llmctl_ag_push(const void* src, llmctl::symm::PeerTable xg, void*
   ag_push_kernel<<<static_cast<int>(grid), kPushThreads, 0, (cudaStream_t)stream>>>(
       (const uint4*)src, (uint4*)mc_xg, xg, dst_off_vec, slab_vec, n_slabs, pads, flag_base, rank * n_slabs, rank,
       world, epoch, counters, src_in_xg);
+  LLMCTL_RETURN_LAST();
+}
+
+namespace llmctl {
+__global__ void __launch_bounds__(32)
+signal_all_kernel(symm::PeerTable pads, int rank, int world, int slot, uint32_t epoch) {
+  if (threadIdx.x < world)
+    symm::signal_set(reinterpret_cast<uint32_t*>(pads.ptr[threadIdx.x]) + slot + rank, epoch);
+}
+}  // namespace llmctl
+
+// Stream-ordered "I am done" announcement: pads[r][slot + rank] = epoch on every rank r (the counterpart of
+// llmctl_signal_wait; used to hand a symmetric buffer back before its next writer may touch it).
+LLMCTL_API int llmctl_signal_all(llmctl::symm::PeerTable pads, int rank, int world, int slot, unsigned int epoch,
+                                 void* stream) {
+  LLMCTL_BEGIN();
+  LLMCTL_REQUIRE(world >= 1 && world <= symm::kMaxRanks && slot >= 0 && slot < 480);
+  signal_all_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(pads, rank, world, slot, epoch);
   LLMCTL_RETURN_LAST();
 }
 

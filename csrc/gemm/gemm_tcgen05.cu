@@ -37,6 +37,14 @@ struct GemmGate {
   int perm;                  // 1: arrival-order permutation of the tile-row blocks
   int rank, world;
   int bpc, bps;              // tile-row blocks per rank chunk / per flag slab
+  // K8 (ZeRO-3 parameter gather consumed by the GEMM): the B operand lives in a symmetric buffer that the owners of
+  // its shards fill over NVLink; flag f covers flat elements [f*b_slab, (f+1)*b_slab) of that buffer.
+  const uint32_t* b_flags;
+  uint32_t b_epoch;
+  long long b_off;           // element offset of B inside the gathered buffer
+  long long b_slab;          // elements per flag
+  long long b_row_stride;    // K-major B: elements between consecutive N rows
+  long long b_span;          // MN-major B: elements of the whole matrix (a tile touches every K row)
 };
 __device__ __forceinline__ int gate_perm(const GemmGate& g, int i) {
   if (!g.perm) return i;
@@ -54,6 +62,20 @@ __device__ __forceinline__ void gate_wait(const GemmGate& g, int m0, int m_end) 
     symm::signal_wait_ge(g.flags + f, g.epoch);
   }
   fence_proxy_async_all();      // generic-proxy flag reads -> async-proxy (TMA) reads of the rows
+}
+template <bool B_MN>
+__device__ __forceinline__ void gate_wait_b(const GemmGate& g, int n0, int n_end) {
+  if (g.b_flags == nullptr || n0 >= n_end) return;
+  long long lo, hi;
+  if (!B_MN) {
+    lo = g.b_off + static_cast<long long>(n0) * g.b_row_stride;
+    hi = g.b_off + static_cast<long long>(n_end) * g.b_row_stride;
+  } else {
+    lo = g.b_off;
+    hi = g.b_off + g.b_span;
+  }
+  for (long long f = lo / g.b_slab; f <= (hi - 1) / g.b_slab; ++f) symm::signal_wait_ge(g.b_flags + f, g.b_epoch);
+  fence_proxy_async_all();
 }
 
 constexpr int kBM = 128;
@@ -142,6 +164,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         const int m0 = mb_ * kBM;
         const int n0 = nb_ * BN;
         gate_wait(gate, m0, min(m0 + kBM, M));
+        gate_wait_b<B_MN>(gate, n0, min(n0 + BN, N));
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&bar_empty[stage], phase ^ 1u);
           uint8_t* sA = smem + stage * Cfg::kStageBytes;
@@ -365,6 +388,7 @@ gemm2_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
         const int m0 = mb_ * (2 * kBM) + static_cast<int>(cta_rank) * kBM;
         const int n0 = nb_ * BN + static_cast<int>(cta_rank) * (BN / 2);
         if (m0 < M) gate_wait(gate, m0, min(m0 + kBM, M));
+        gate_wait_b<B_MN>(gate, n0, min(n0 + BN / 2, N));
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&bar_empty[stage], phase ^ 1u);
           uint8_t* sA = smem + stage * Cfg::kStageBytes;
@@ -681,4 +705,24 @@ LLMCTL_API int llmctl_gemm_bf16_gated(const void* A, const void* B, void* C, int
   g.rank = rank;
   g.world = world;
   return gemm_bf16_impl(A, B, C, M, N, K, lda, ldb, ldc, 0, b_mn, out_fp32, beta, tile_n, max_ctas, stream, g);
+}
+
+// K8 consumer: the same GEMM, with the B operand (a ZeRO-3 parameter matrix inside a gathered symmetric buffer) read
+// tile by tile as its shards arrive: flag  b_flags[(b_off + element) / b_slab]  (local signal pad, raised by the shard
+// owners' llmctl_ag_push) must have reached `epoch` before the tile's rows are loaded.  ldb must equal the row pitch of
+// B inside the buffer.
+LLMCTL_API int llmctl_gemm_bf16_bgated(const void* A, const void* B, void* C, int M, int N, int K,
+                                       long long lda, long long ldb, long long ldc, int a_mn, int b_mn,
+                                       int out_fp32, int beta, int tile_n, int max_ctas,
+                                       const unsigned int* b_flags, unsigned int epoch, long long b_off,
+                                       long long b_slab, void* stream) {
+  LLMCTL_REQUIRE(b_flags != nullptr && b_slab > 0 && b_off >= 0);
+  GemmGate g{};
+  g.b_flags = b_flags;
+  g.b_epoch = epoch;
+  g.b_off = b_off;
+  g.b_slab = b_slab;
+  g.b_row_stride = ldb;
+  g.b_span = static_cast<long long>(K) * ldb;
+  return gemm_bf16_impl(A, B, C, M, N, K, lda, ldb, ldc, a_mn, b_mn, out_fp32, beta, tile_n, max_ctas, stream, g);
 }

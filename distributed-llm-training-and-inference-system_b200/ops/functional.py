@@ -307,9 +307,11 @@ def swiglu(gate_up: torch.Tensor) -> torch.Tensor:
 # ------------------------------------------------------------------------------------------------
 def gemm_raw(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = False,
              out: Optional[torch.Tensor] = None, out_dtype: torch.dtype = torch.bfloat16,
-             accumulate: bool = False, tile_n: int = 0, max_ctas: int = 0) -> torch.Tensor:
+             accumulate: bool = False, tile_n: int = 0, max_ctas: int = 0, b_gate: Optional[dict] = None) -> torch.Tensor:
     """Direct call of the tcgen05 GEMM.  Shapes follow include/llmctl_b200.h:
-    ``a_mn=False``: a is [M,K]; ``a_mn=True``: a is [K,M].  ``b_mn=False``: b is [N,K]; else [K,N]."""
+    ``a_mn=False``: a is [M,K]; ``a_mn=True``: a is [K,M].  ``b_mn=False``: b is [N,K]; else [K,N].
+    ``b_gate`` (K8): ``b`` lives in a ZeRO-3 gather buffer that is still being filled; the kernel waits per tile for the
+    arrival flags of the weight rows it loads (keys: flags, epoch, off, slab)."""
     assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16 and a.is_cuda
     assert a.stride(1) == 1 and b.stride(1) == 1
     if a_mn:
@@ -326,6 +328,12 @@ def gemm_raw(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool
         out = torch.empty(M, N, dtype=out_dtype, device=a.device)
     else:
         assert out.shape == (M, N) and out.stride(1) == 1
+    if b_gate is not None:
+        native.call("llmctl_gemm_bf16_bgated", a.data_ptr(), b.data_ptr(), out.data_ptr(), M, N, K,
+                    a.stride(0), b.stride(0), out.stride(0), int(a_mn), int(b_mn),
+                    int(out.dtype == torch.float32), int(accumulate), tile_n or _cfg.gemm_tile_n, max_ctas,
+                    b_gate["flags"], b_gate["epoch"], b_gate["off"], b_gate["slab"], native.stream_ptr())
+        return out
     native.call("llmctl_gemm_bf16", a.data_ptr(), b.data_ptr(), out.data_ptr(), M, N, K,
                 a.stride(0), b.stride(0), out.stride(0), int(a_mn), int(b_mn),
                 int(out.dtype == torch.float32), int(accumulate), tile_n or _cfg.gemm_tile_n, max_ctas,
@@ -346,7 +354,15 @@ class _LinearFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, w):
-        y = gemm_raw(x, w)
+        gate = getattr(w, "_k8_gate", None)
+        if gate is not None:
+            # ZeRO-3 (K8): the weight is still arriving over NVLink; the GEMM consumes it slab by slab, then the rest
+            # of the unit is awaited before anything else touches it
+            w._k8_gate = None
+            y = gemm_raw(x, w, b_gate=gate)
+            gate["after"]()
+        else:
+            y = gemm_raw(x, w)
         ctx.save_for_backward(x, w)
         return y
 
@@ -402,6 +418,11 @@ def gemm_skinny(x: torch.Tensor, w: torch.Tensor, out: Optional[torch.Tensor] = 
 
 def linear(x: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
     """``x @ w.T`` (no bias).  x: [..., K], w: [N, K]."""
+    gate = getattr(w, "_k8_gate", None)
+    if gate is not None and not (_use_native(x, "gemm") and w.dtype == torch.bfloat16 and x.reshape(-1, x.shape[-1]).shape[0] > SKINNY_MAX_ROWS
+                                 and w.shape[0] % 8 == 0):
+        w._k8_gate = None          # not the gated GEMM path: wait for the whole unit first
+        gate["after"]()
     if _use_native(x, "gemm") and w.dtype == torch.bfloat16:
         shape = x.shape
         x2 = x.reshape(-1, shape[-1])
@@ -412,6 +433,10 @@ def linear(x: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
             return gemm_skinny(x2, w).view(*shape[:-1], w.shape[0])
         if _gemm_ok(x2, w) and w.shape[0] % 8 == 0:
             return _LinearFn.apply(x2, w).view(*shape[:-1], w.shape[0])
+    gate = getattr(w, "_k8_gate", None)
+    if gate is not None:
+        w._k8_gate = None
+        gate["after"]()
     return F.linear(x, w)
 
 

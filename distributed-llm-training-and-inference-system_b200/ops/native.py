@@ -42,6 +42,7 @@ _SIGNATURES = {
     "llmctl_cross_entropy_partial": [c_void_p, c_ll, c_void_p, c_void_p, c_int, c_int, c_ll, c_void_p],
     "llmctl_cross_entropy_finalize": [c_void_p, c_ll, c_void_p, c_void_p, c_int, c_int, c_ll, c_ll, c_float, c_void_p, c_void_p],
     "llmctl_gemm_bf16": [c_void_p] * 3 + [c_int] * 3 + [c_ll] * 3 + [c_int] * 6 + [c_void_p],
+    "llmctl_gemm_bf16_bgated": [c_void_p] * 3 + [c_int] * 3 + [c_ll] * 3 + [c_int] * 6 + [c_void_p, ctypes.c_uint, c_ll, c_ll, c_void_p],
     "llmctl_gemm_skinny_bf16": [c_void_p] * 3 + [c_int] * 3 + [c_ll] * 3 + [c_void_p, c_ll, c_void_p, c_int, c_int, c_void_p],
 }
 

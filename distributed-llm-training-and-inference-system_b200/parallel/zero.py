@@ -190,37 +190,73 @@ class ParamUnit:
 
 
 class PeerParamGatherer:
-    """K8 (first step): ZeRO-3 parameter all-gather over NVLink peer memory with our own pull kernel
-    (``llmctl_allgather_pull``) instead of NCCL, plus prefetch of the next unit on a side stream so the transfer
-    overlaps the current unit's GEMMs.  Units are gathered into a small pool of symmetric buffers (each as large
-    as the biggest unit); a buffer is recycled when its unit is released.  The kernel's own end-of-kernel
-    all-rank handshake makes immediate reuse safe.  (Fusing the gather into the first consuming GEMM, K1-style
-    with the B operand gathered, is listed in DESIGN.md §7.)"""
+    """K8: ZeRO-3 parameter all-gather over NVLink peer memory, consumed by the GEMM as it arrives.
+
+    Units are gathered into a small pool of symmetric buffers (each as large as the biggest unit).  Every rank PUSHES
+    its parameter shard into all peers' copy of the buffer (``llmctl_ag_push``: NVLS ``multimem.st`` or P2P stores) in
+    ``SLABS`` slabs and raises a per-slab epoch flag on every rank; nothing on the compute stream waits for the gather
+    as a whole:
+      * the first GEMM of a transformer block (QKV) runs in B-gated mode (``llmctl_gemm_bf16_bgated``): its TMA producer
+        waits per tile for the flags covering the weight rows it is about to load, so the math on the slabs that have
+        landed overlaps the transfer of the rest;
+      * small non-GEMM parameters (norm weights) wait for their own slab only, everything after the first GEMM waits
+        for the remaining flags with a one-warp kernel (``llmctl_signal_wait``).
+    The next unit (forward: k+1, backward: k-1) is pushed on a side stream while the current one computes, so in
+    steady state the flags are already up when the GEMM asks.  A pool buffer is handed back with a cross-rank "done
+    reading" flag exchange (``llmctl_signal_all``) and only rewritten once every peer has released it."""
+
+    SLABS = 4
+    ARRIVE_BASE = 64          # pad slots [64, 64 + world * SLABS): slab (r, s) of the current occupant has arrived
+    FREE_BASE = 128           # pad slots [128, 128 + world): rank r finished reading the previous occupant
 
     def __init__(self, units, st: ParallelState, pool: int = 4):
-        from ..comms.collectives import PeerCollectives
+        import ctypes
+        from ..comms.symm import PeerTable, SymmBuffer
+        from ..ops import native
         self.st = st
         self.units = units
         self.max_numel = max(u.numel for u in units)
-        self.pool = [PeerCollectives(self.max_numel, st.dp_group, st.device) for _ in range(pool)]
+        self.pool = [SymmBuffer(self.max_numel, torch.bfloat16, st.dp_group, st.device) for _ in range(pool)]
+        self.rank, self.world = self.pool[0].rank, self.pool[0].world
+        self.ep_push = [0] * pool
+        self.ep_free = [0] * pool
+        self.counters = torch.zeros(64, dtype=torch.int32, device=st.device)
         self.free = list(range(pool))
         self.owner: Dict[str, int] = {}
         self.pending: Dict[str, torch.cuda.Event] = {}
         self.stream = torch.cuda.Stream(device=st.device)
         self.order = {u.name: i for i, u in enumerate(units)}
         self.direction = +1
+        import os
+        self.use_multicast = os.environ.get("LLMCTL_K8_NVLS", "1") != "0"
+        self.gate_first_gemm = os.environ.get("LLMCTL_K8_GATED_GEMM", "1") != "0"
+        self.stats = {"pushes": 0, "gated_gemms": 0}
+        vp, i32, i64, u32 = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_uint
+        native.register_signature("llmctl_ag_push", [vp, PeerTable, vp, i32, i32, i32, PeerTable, i32, i32, i32, u32, vp, i32, i32, vp])
+        native.register_signature("llmctl_signal_all", [PeerTable, i32, i32, i32, u32, vp])
+        native.register_signature("llmctl_signal_wait", [PeerTable, i32, i32, i32, u32, vp])
+        torch.cuda.synchronize(st.device)
+        self.pool[0].barrier()
 
+    # ---- producer side ---------------------------------------------------------------------------------------
     def _launch(self, u: "ParamUnit", stream) -> None:
-        slot = self.free.pop()
+        from ..ops import native
+        slot = self.free.pop(0)
         self.owner[u.name] = slot
-        pc = self.pool[slot]
+        buf = self.pool[slot]
+        self.ep_push[slot] += 1
         with torch.cuda.stream(stream):
-            chunk = u.shard_numel
-            pc.buf.tensor[pc.rank * chunk:(pc.rank + 1) * chunk].copy_(u.param_shard, non_blocking=True)
-            pc.all_gather_(chunk)
+            if self.ep_free[slot] > 0:          # every peer must have released this buffer's previous occupant
+                native.call("llmctl_signal_wait", buf.pads, self.rank, self.world, self.FREE_BASE, self.ep_free[slot],
+                            stream.cuda_stream)
+            mc = buf.multicast_ptr if self.use_multicast else 0
+            native.call("llmctl_ag_push", u.param_shard.data_ptr(), buf.peers, mc or None, self.SLABS,
+                        u.shard_numel // self.SLABS, 1, buf.pads, self.ARRIVE_BASE, self.rank, self.world,
+                        self.ep_push[slot], self.counters.data_ptr(), 0, 0, stream.cuda_stream)
             ev = torch.cuda.Event()
             ev.record(stream)
         self.pending[u.name] = ev
+        self.stats["pushes"] += 1
 
     def prefetch(self, u: "ParamUnit") -> None:
         if u.name in self.owner or u.flat_param is not None or not self.free:
@@ -228,27 +264,89 @@ class PeerParamGatherer:
         self.stream.wait_stream(torch.cuda.current_stream(self.st.device))
         self._launch(u, self.stream)
 
+    # ---- consumer side ---------------------------------------------------------------------------------------
+    def _wait_flags(self, buf, first: int, count: int, epoch: int) -> None:
+        from ..ops import native
+        s = native.stream_ptr()
+        while count > 0:
+            n = min(count, 8)
+            native.call("llmctl_signal_wait", buf.pads, self.rank, n, self.ARRIVE_BASE + first, epoch, s)
+            first, count = first + n, count - n
+
+    def _flag_of(self, u: "ParamUnit", elem: int) -> int:
+        return elem // (u.shard_numel // self.SLABS)
+
     def gather(self, u: "ParamUnit") -> torch.Tensor:
         cur = torch.cuda.current_stream(self.st.device)
         if u.name not in self.owner:
             if not self.free:
                 raise RuntimeError("ZeRO-3 gather pool exhausted; release units before gathering more")
-            self._launch(u, cur)
-        ev = self.pending.pop(u.name, None)
-        if ev is not None:
-            cur.wait_event(ev)
-        flat = self.pool[self.owner[u.name]].buf.tensor[:u.numel]
-        # prefetch the unit that will be needed next (forward: next unit, backward: previous unit)
+            self.stream.wait_stream(cur)
+            self._launch(u, self.stream)
+        self.pending.pop(u.name, None)
+        slot = self.owner[u.name]
+        buf, epoch = self.pool[slot], self.ep_push[slot]
+        flat = buf.tensor[:u.numel]
+        n_flags = self.world * self.SLABS
+        # forward only: in backward the first consumer of a block is not its QKV projection
+        gate_param = self._first_gemm_weight(u) if (self.gate_first_gemm and self.direction > 0) else None
+        if gate_param is None:
+            self._wait_flags(buf, 0, n_flags, epoch)            # no gated consumer: the whole unit must have landed
+        else:
+            # parameters that are read before the first GEMM (the block's first norm weight) wait for their own slab
+            idx = next(i for i, p in enumerate(u.params) if p is gate_param)
+            seen = set()
+            for p, o in zip(u.params[:idx], u.offsets[:idx]):
+                for f in range(self._flag_of(u, o), self._flag_of(u, o + p.numel() - 1) + 1):
+                    if f not in seen:
+                        self._wait_flags(buf, f, 1, epoch)
+                        seen.add(f)
+
+            def after_first_gemm(buf=buf, epoch=epoch, n_flags=n_flags):
+                self._wait_flags(buf, 0, n_flags, epoch)        # everything else of the unit, before its next consumer
+                self.stats["gated_gemms"] += 1
+            gate_param._k8_gate = {"flags": buf.signal_ptrs[self.rank] + 4 * self.ARRIVE_BASE, "epoch": epoch,
+                                   "off": u.offsets[idx], "slab": u.shard_numel // self.SLABS, "after": after_first_gemm}
+        # push the unit that will be needed next (forward: next unit, backward: previous unit)
         i = self.order[u.name] + self.direction
         if 0 <= i < len(self.units):
             self.prefetch(self.units[i])
         return flat
 
+    @staticmethod
+    def _first_gemm_weight(u: "ParamUnit"):
+        """The weight of the first GEMM a transformer block runs (QKV projection), if this unit is such a block and
+        the consumer is the native GEMM of a non-TP model; None otherwise (the unit is then awaited as a whole)."""
+        from ..ops import functional as ops
+        attn = getattr(u.module, "attn", None)
+        qkv = getattr(attn, "qkv", None) if attn is not None else None
+        w = getattr(qkv, "weight", None)
+        if (w is None or not hasattr(u.module, "norm1") or hasattr(w, "tp_shard_dim") and u.st.tp > 1
+                or ops.kernel_config().gemm != "native" or w.dtype != torch.bfloat16):
+            return None
+        return w if any(w is p for p in u.params) else None
+
+    def finish_gate(self, u: "ParamUnit") -> None:
+        """Called when a unit is released: a gate nobody consumed (e.g. the block ran through another path) must not
+        leak to the next occupant; its pending waits are issued so the buffer is not handed back while data is in flight."""
+        for p in u.params:
+            g = getattr(p, "_k8_gate", None)
+            if g is not None:
+                p._k8_gate = None
+                g["after"]()
+
     def release(self, u: "ParamUnit") -> None:
+        from ..ops import native
         slot = self.owner.pop(u.name, None)
-        if slot is not None:
-            self.pending.pop(u.name, None)
-            self.free.append(slot)
+        if slot is None:
+            return
+        self.finish_gate(u)
+        self.pending.pop(u.name, None)
+        buf = self.pool[slot]
+        self.ep_free[slot] += 1
+        native.call("llmctl_signal_all", buf.pads, self.rank, self.world, self.FREE_BASE, self.ep_free[slot],
+                    native.stream_ptr())
+        self.free.append(slot)
 
 
 class ZeroOptimizer:

@@ -147,6 +147,15 @@ int llmctl_allreduce_multimem(void* mc, long long n, llmctl_peer_table pads, int
  * at pads[*][flag_base + row / rows_per_flag]; the consumer is the tcgen05 GEMM whose TMA producer waits per tile for
  * the flags of the rows it reads (llmctl_gemm_bf16_gated; flags = this rank's pad + flag_base). counters: >= 32
  * zeroed uint32 in local memory. */
+/* K8: GEMM whose B operand (a ZeRO-3 parameter matrix inside a gather buffer that its shard owners are still filling
+ * with llmctl_ag_push) is consumed as it arrives: before a tile's weight rows are loaded, the flags
+ * b_flags[(b_off + element) / b_slab] must have reached `epoch`.  llmctl_signal_all / llmctl_signal_wait hand a gather
+ * buffer back and forth between its readers and its next writers. */
+int llmctl_gemm_bf16_bgated(const void* A, const void* B, void* C, int M, int N, int K, long long lda, long long ldb,
+                            long long ldc, int a_mn, int b_mn, int out_fp32, int beta, int tile_n, int max_ctas,
+                            const unsigned int* b_flags, unsigned int epoch, long long b_off, long long b_slab,
+                            void* stream);
+int llmctl_signal_all(llmctl_peer_table pads, int rank, int world, int slot, unsigned int epoch, void* stream);
 int llmctl_ag_gemm(llmctl_peer_table xg, void* mc_xg, const void* W, void* Y, int M, int N, int K, long long ldw,
                    long long ldy, int w_mn, int rows_per_flag, llmctl_peer_table pads, int flag_base, int rank,
                    int world, unsigned int epoch, unsigned int* counters, int push_ctas, int tile_n,

@@ -325,7 +325,8 @@ def _zero_traj(stage, comm, steps=4, tp=1):
         losses.append((eng._reduce_scalar(o["loss"]), float(o["grad_norm"])))
     with eng.optimizer.full_params_context():
         p_end = torch.cat([p.detach().float().reshape(-1) for p in eng.model.parameters()])
-    info = {"native": eng.optimizer.native_comm is not None, "gatherer": eng.optimizer.gatherer is not None}
+    info = {"native": eng.optimizer.native_comm is not None, "gatherer": eng.optimizer.gatherer is not None,
+            "k8": dict(eng.optimizer.gatherer.stats) if eng.optimizer.gatherer is not None else None}
     torch.cuda.synchronize(); dist.barrier()
     from llmctl_b200.comms import fused
     fused.shutdown()
@@ -339,13 +340,15 @@ def _compare_zero(out, key, stage, tp=1):
     assert info["native"], "K7 path was not enabled"
     if stage >= 3:
         assert info["gatherer"], "peer gatherer was not enabled"
+        if tp == 1:      # every block's QKV GEMM consumed its weight through the arrival flags (K8)
+            assert info["k8"]["gated_gemms"] >= 4 * 2, info
     for (la, ga), (lb, gb) in zip(ref_l, nat_l):
         assert abs(la - lb) < 1e-2 * max(1, abs(la)), f"loss nccl {ref_l} native {nat_l}"
         assert abs(ga - gb) < 2e-2 * max(1, abs(ga)), f"gnorm nccl {ref_l} native {nat_l}"
     # gate relative to the size of the update itself: a path that skipped (or halved) the update fails
     rel = ((nat_d - ref_d).norm() / ref_d.norm()).item()
     assert ref_d.norm().item() > 0 and rel < 0.1, f"update differs from the NCCL path by {rel:.3f} of its size"
-    out[key] = {"nccl": ref_l, "native": nat_l, "update_rel_diff": rel}
+    out[key] = {"nccl": ref_l, "native": nat_l, "update_rel_diff": rel, "k8": info.get("k8")}
 
 
 def case_zero_native(out):
