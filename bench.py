@@ -50,6 +50,7 @@ def parse_args():
     ap.add_argument("--activation-checkpoint", default="none")
     ap.add_argument("--grad-accum", type=int, default=None, help="micro-batches per step (default 1; 2*pp with a pipeline)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--host-profile", default=None, help="write a cProfile of the timed steps (rank 0) to this file")
     ap.add_argument("--no-extras", action="store_true", help="8 GPUs: skip the TP8+SP / ZeRO-3 / 13B TP4xPP2 arms")
     ap.add_argument("--extras-selftest", action="store_true", help="2 GPUs: run scaled-down extra arms (plumbing check)")
     ap.add_argument("--extra-steps", type=int, default=20)
@@ -189,12 +190,31 @@ def measure(args, K: int, W: int, with_e2e: bool = True, min_timed_s: float = 0.
         sampler.start()
     launches0 = native.launch_count
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    prof = None
+    if getattr(args, "host_profile", None) and st.rank == 0:
+        import cProfile
+        prof = cProfile.Profile()
     ev0.record()
+    t_host0 = time.perf_counter()
+    if prof:
+        prof.enable()
     for i in range(K):
         loss = step_resident(W + i)
+    if prof:
+        prof.disable()
+    host_ms = (time.perf_counter() - t_host0) * 1e3 / K     # time to ENQUEUE a step; ~ms_per_step means the host is the limit
     eng.optimizer.sync_params()       # the last step's parameter publication (side stream) belongs to the timed region
     ev1.record()
     barrier()
+    if prof:
+        import io
+        import pstats
+        buf = io.StringIO()
+        st_ = pstats.Stats(prof, stream=buf)
+        st_.sort_stats("tottime").print_stats(30)
+        st_.sort_stats("cumulative").print_stats(45)
+        Path(args.host_profile).parent.mkdir(parents=True, exist_ok=True)
+        Path(args.host_profile).write_text(buf.getvalue())
     launches = native.launch_count - launches0
     clocks = sampler.stop() if sampler else {}
     ms = torch.tensor([ev0.elapsed_time(ev1)], device=dev, dtype=torch.float64)
@@ -279,6 +299,7 @@ def measure(args, K: int, W: int, with_e2e: bool = True, min_timed_s: float = 0.
                    "kernels": paths},
         "model_tflops_per_gpu": value * flops_tok / world / 1e12,
         "final_loss": final_loss, "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
+        "host_enqueue_ms_per_step": round(host_ms, 2),
     }
     # ---------------- teardown: the next arm builds its own mesh ----------------
     barrier()

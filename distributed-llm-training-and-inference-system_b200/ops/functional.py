@@ -69,7 +69,7 @@ _scratch_cache: dict = {}
 
 def _scratch(device: torch.device, nfloats: int, tag: str = "") -> torch.Tensor:
     """Per-(device, stream, tag) fp32 scratch buffer, grown geometrically and reused across calls."""
-    key = (device.index, torch.cuda.current_stream(device).cuda_stream, tag)
+    key = (device.index, native.stream_ptr(), tag)
     buf = _scratch_cache.get(key)
     if buf is None or buf.numel() < nfloats:
         buf = torch.empty(max(nfloats, 1), dtype=torch.float32, device=device)
