@@ -50,6 +50,7 @@ def launch(
     inject_fault: Optional[str] = typer.Option(None, "--inject-fault", help="debug: rank:step:kill|hang|nan"),
     collective_timeout: Optional[int] = typer.Option(None, "--collective-timeout", help="Seconds a collective may wait before the rank fails (default 1800)"),
     prometheus_port: Optional[int] = typer.Option(None, "--prometheus-port", help="Rank 0 serves llmctl_training_* metrics on this port"),
+    no_final_save: bool = typer.Option(False, "--no-final-save", help="Do not write <output-dir>/final at the end (timing runs)"),
     dry_run: bool = typer.Option(False, "--dry-run", help="Show the resolved launch, start nothing"),
 ):
     """Launch a training run."""
@@ -83,6 +84,8 @@ def launch(
         argv.append("--sequence-parallel")
     if g.deterministic:
         argv.append("--deterministic")
+    if no_final_save:
+        argv.append("--no-final-save")
 
     t = Table(title="Training launch"); t.add_column("Setting"); t.add_column("Value")
     for k, v in (("launcher", launcher), ("nodes", nodes), ("gpus per node", gpus_per_node), ("plan", plan),

@@ -85,6 +85,7 @@ class TrainingConfig:
     total_steps: Optional[int] = None        # scheduler horizon (defaults to max_steps / epochs)
     async_checkpoint: bool = False
     inject_fault: Optional[str] = None
+    save_final: bool = True                  # write <output_dir>/final at the end (--no-final-save: timing runs of big models)
     max_nonfinite_windows: int = 3       # consecutive non-finite logging windows before the run aborts (0 = never)
     collective_timeout_s: int = 1800     # a collective that waits longer fails the rank (-> restart under --max-restarts)
     metrics_jsonl: bool = True
@@ -424,7 +425,8 @@ class TrainingEngine:
             self.epoch = step // max(c.steps_per_epoch, 1)
             for cb in self.step_callbacks:
                 cb(self, out)
-        self.save_checkpoint(final=True)
+        if c.save_final:
+            self.save_checkpoint(final=True)
         ckpt_io.wait_for_async_save()
         if profiler is not None:
             profiler.stop()

@@ -45,6 +45,7 @@ def parse_args(argv=None):
     ap.add_argument("--deterministic", action="store_true", default=None)
     ap.add_argument("--sequence-parallel", dest="sequence_parallel", action="store_true", default=None)
     ap.add_argument("--async-checkpoint", dest="async_checkpoint", action="store_true", default=None)
+    ap.add_argument("--no-final-save", dest="save_final", action="store_false", default=None)
     return ap.parse_args(argv)
 
 
