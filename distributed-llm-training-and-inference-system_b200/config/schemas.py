@@ -326,7 +326,20 @@ def resolve_training_config(preset: Optional[Union[str, Path]] = None, plan: Opt
             if prof.get("enable"):
                 out["trace_schedule"] = prof.get("schedule", "step(100)")
     if plan:
-        pl = load_plan(plan).parallelism
+        pf = load_plan(plan)
+        pl = pf.parallelism
+        # the plan was costed for one model (and sequence length): train that model unless a preset / flag names
+        # another (the reference stores the plan path and never reads it: reference llmctl/runtime/launcher.py:34)
+        if "model_name_or_path" not in out:
+            mfile = pf.metadata.get("model_file")
+            if mfile and Path(mfile).exists():
+                out["model_name_or_path"] = str(mfile)
+            elif mfile and (Path(plan).resolve().parent / mfile).exists():
+                out["model_name_or_path"] = str(Path(plan).resolve().parent / mfile)
+            elif pf.model.get("name"):
+                out["model_name_or_path"] = str(pf.model["name"])
+        if "seq_len" not in out and pf.metadata.get("seq_len"):
+            out["seq_len"] = int(pf.metadata["seq_len"])
         out.update(tensor_parallel=pl.tensor_parallel, pipeline_parallel=pl.pipeline_parallel,
                    zero_stage=pl.zero_stage, sequence_parallel=pl.sequence_parallel,
                    activation_checkpoint=pl.activation_checkpoint, batch_size=pl.micro_batch_size)

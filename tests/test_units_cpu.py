@@ -3,6 +3,7 @@ plugin registry, checkpoint GC, LR schedule, export re-sharding, roofline."""
 import json
 import math
 import time
+from pathlib import Path
 
 import pytest
 import torch
@@ -340,3 +341,27 @@ def test_gguf_writer_round_trip(tmp_path):
             assert torch.equal(tensors["blk.0.attn_q.weight"][h * hd + 2 * j + 1], q[h * hd + hd // 2 + j])
     assert torch.equal(tensors["blk.0.attn_v.weight"], full["blocks.0.attn.qkv.weight"][2 * H:])
     assert torch.equal(tensors["blk.0.ffn_up.weight"], full["blocks.0.mlp.up.weight"][ffn:])
+
+
+def test_train_consumes_the_model_named_by_the_plan(tmp_path):
+    """`llmctl train --plan P` trains the model the plan was computed for (model file, else the name recorded in the
+    plan's [model] table) at the plan's sequence length, unless a flag overrides it."""
+    import json
+    from llmctl_b200.config.schemas import resolve_training_config
+    root = Path(__file__).resolve().parent.parent
+    plan = root / "configs" / "plans" / "gpt-13b-b200x8-auto-pp2.toml"
+    import os
+    cwd = os.getcwd()
+    os.chdir(root)
+    try:
+        r = resolve_training_config(None, plan, {"max_steps": 3})
+        assert r["model_name_or_path"].endswith("gpt-13b.json") and r["seq_len"] == 2048
+        assert (r["tensor_parallel"], r["pipeline_parallel"], r["sequence_parallel"]) == (4, 2, True)
+        assert resolve_training_config(None, plan, {"model_name_or_path": "gpt-125m"})["model_name_or_path"] == "gpt-125m"
+    finally:
+        os.chdir(cwd)
+    # a plan whose model file is gone falls back to the model name stored in the plan
+    txt = plan.read_text().replace('model_file = "configs/models/gpt-13b.json"', 'model_file = "nowhere/x.json"')
+    p2 = tmp_path / "p.toml"
+    p2.write_text(txt)
+    assert resolve_training_config(None, p2, {})["model_name_or_path"] == "gpt-13b"
