@@ -70,6 +70,12 @@ gemm_rs_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const int tiles_per_chunk = m_per_chunk * num_n;
   const int num_tiles = tiles_per_chunk * a.world;
   const int num_kb = (a.K + kFBK - 1) / kFBK;
+  // Each CTA takes a CONTIGUOUS range of the chunk-major tile list: its tiles share a destination (and a B panel), so
+  // an epilogue warp publishes once per destination instead of once per tile — the system-scope fence in front of
+  // the publication waits for the warp's outstanding NVLink stores and used to stall the epilogue after every tile —
+  // and at any moment the CTAs together feed all destinations, not one.
+  const int t_begin = static_cast<int>(static_cast<long long>(cta) * num_tiles / n_cta);
+  const int t_end = static_cast<int>(static_cast<long long>(cta + 1) * num_tiles / n_cta);
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < kFStages; ++i) {
@@ -106,7 +112,7 @@ gemm_rs_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = cta; tile < num_tiles; tile += n_cta) {
+      for (int tile = t_begin; tile < t_end; ++tile) {
         int crank, m0, n0, m_end;
         decode(tile, crank, m0, n0, m_end);
         for (int kb = 0; kb < num_kb; ++kb) {
@@ -136,7 +142,7 @@ gemm_rs_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       uint32_t phase = 0;
       int acc = 0;
       uint32_t aphase = 0;
-      for (int tile = cta; tile < num_tiles; tile += n_cta) {
+      for (int tile = t_begin; tile < t_end; ++tile) {
         mbar_wait(&bar_tempty[acc], aphase ^ 1u);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * kFBN);
@@ -166,9 +172,30 @@ gemm_rs_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int q = warp & 3;
     int acc = 0;
     uint32_t aphase = 0;
-    for (int tile = cta; tile < num_tiles; tile += n_cta) {
+    int cur_dest = -1;
+    uint32_t unpublished = 0;       // tiles of cur_dest whose stores this warp has issued but not yet announced
+    // all of this warp's remote stores -> system fence -> warp converges -> lane 0 counts them in; the last
+    // (tile, warp) pair of a destination raises that destination's flag
+    auto publish = [&]() {
+      if (unpublished == 0) return;
+      __threadfence_system();
+      __syncwarp();
+      if (lane == 0) {
+        const uint32_t done = atomicAdd(&local_flags[cur_dest], unpublished) + unpublished;
+        if (done == static_cast<uint32_t>(tiles_per_chunk * 4)) {
+          atomicExch(&local_flags[cur_dest], 0u);
+          signal_set(reinterpret_cast<uint32_t*>(pads.ptr[cur_dest]) + 8 + a.rank, a.epoch);
+        }
+      }
+      unpublished = 0;
+    };
+    for (int tile = t_begin; tile < t_end; ++tile) {
       int crank, m0, n0, m_end;
       decode(tile, crank, m0, n0, m_end);
+      if (crank != cur_dest) {
+        publish();
+        cur_dest = crank;
+      }
       mbar_wait(&bar_tfull[acc], aphase);
       tc_fence_after();
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(acc * kFBN);
@@ -210,23 +237,13 @@ gemm_rs_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
       }
       tc_fence_before();
-      {
-        // count finished (tile, warp) pairs per destination; the last one raises the destination's flag.
-        // Order: every lane's remote stores -> system fence -> warp converges -> lane 0 publishes.
-        __threadfence_system();
-        __syncwarp();
-        if (lane == 0) {
-          const uint32_t done = atomicAdd(&local_flags[crank], 1u) + 1u;
-          if (done == static_cast<uint32_t>(tiles_per_chunk * 4)) {
-            atomicExch(&local_flags[crank], 0u);
-            signal_set(reinterpret_cast<uint32_t*>(pads.ptr[crank]) + 8 + a.rank, a.epoch);
-          }
-        }
-      }
+      __syncwarp();
+      ++unpublished;
       if (lane == 0) mbar_arrive(&bar_tempty[acc]);
       acc ^= 1;
       if (acc == 0) aphase ^= 1u;
     }
+    publish();
   }
 
   tc_fence_before();
