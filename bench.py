@@ -398,7 +398,7 @@ def main():
         res = run_reference(args)
     else:
         res = run_native(args)
-    if res is not None:
+    if res is not None and (int(os.environ.get("RANK", "0")) == 0 or "unavailable" not in res):
         print(json.dumps(res), flush=True)
     _shutdown()
 
