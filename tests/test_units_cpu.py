@@ -365,3 +365,24 @@ def test_train_consumes_the_model_named_by_the_plan(tmp_path):
     p2 = tmp_path / "p.toml"
     p2.write_text(txt)
     assert resolve_training_config(None, p2, {})["model_name_or_path"] == "gpt-13b"
+
+
+def test_measured_cost_model_reproduces_the_round2_b200_runs():
+    """The planner's step-time model against what this framework measured on 8 x B200 (profiles/bench_n8_with_extras.json,
+    profiles/train_13b_plan_cli/, profiles/bench_n1.json): every configuration within 15%."""
+    from llmctl_b200.models.config import get_preset
+    from llmctl_b200.partition.planner import HardwareNumbers, MeasuredCostModel
+    hw = HardwareNumbers(gpus=8)
+    points = [  # model, seq, (tp, pp, dp, zero, micro_batch, sp, ckpt, n_micro), measured ms
+        ("gpt-7b", 512, (1, 1, 8, 1, 8, False, "none", 1), 173.2), ("gpt-7b", 512, (8, 1, 1, 0, 8, True, "none", 1), 48.2),
+        ("gpt-7b", 512, (1, 1, 8, 3, 8, False, "none", 1), 188.0), ("gpt-13b", 2048, (4, 2, 1, 0, 2, True, "none", 8), 489.0),
+        ("gpt-13b", 2048, (4, 2, 1, 0, 1, True, "none", 16), 632.0), ("gpt-1b", 512, (2, 1, 1, 0, 4, True, "none", 1), 21.0)]
+    for name, seq, args, measured in points:
+        t = MeasuredCostModel(get_preset(name), hw, seq_len=seq).step_time(*args)["total"] * 1e3
+        assert abs(t - measured) / measured < 0.15, (name, args, t, measured)
+    t1 = MeasuredCostModel(get_preset("gpt-7b"), HardwareNumbers(gpus=1), seq_len=512).step_time(1, 1, 1, 0, 8, False, "none", 1)["total"] * 1e3
+    assert abs(t1 - 179.0) / 179.0 < 0.1
+    # fewer, larger micro-batches win under a pipeline once the per-layer overhead is counted
+    m = MeasuredCostModel(get_preset("gpt-13b"), hw, seq_len=2048)
+    best = m.search(global_batch=16, pins={"pipeline_parallel": 2, "tensor_parallel": 4})[0]
+    assert best.micro_batch_size >= 2 and best.sequence_parallel, best
