@@ -2,8 +2,8 @@
 
 ``attention(q, k, v)`` takes ``[B, S, H, D]`` views (typically slices of the packed qkv activation) and
 dispatches to the tcgen05 flash-attention kernels (``csrc/attention``) when they are built and the shape is
-supported (bf16, head_dim 128; causal sequences of any length — ragged ones are padded to the 128-token tile), else to
-PyTorch SDPA (head_dim 64 models such as gpt-125m, non-causal ragged shapes, CPU).
+supported (bf16, head_dim 128, or 64 zero-padded to 128; causal sequences of any length — ragged ones are padded to the
+128-token tile), else to PyTorch SDPA (other head sizes, non-causal ragged shapes, CPU).
 
 Reference: the reference never calls attention itself — HF modules pick SDPA/eager behind
 ``self.model(**batch)`` (reference llmctl/runtime/engine.py:284); its tuner benchmarks a naive
@@ -96,6 +96,13 @@ def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, causal: bool = 
     if _native_ok(q, k, v):
         return _FlashAttnFn.apply(q, k, v, scale, causal)
     S = q.shape[1]
+    if (q.shape[-1] == 64 and q.is_cuda and q.dtype == torch.bfloat16 and kernel_config().attention == "native"
+            and native.has_symbol("llmctl_flash_attn_fwd") and (causal or S % 128 == 0)):
+        # head_dim 64 (gpt-125m class models): the kernel's tiles are 128 wide, so the head is zero-padded to 128 —
+        # zero q/k columns add nothing to the scores, zero v columns produce zero outputs that are sliced away.  Twice
+        # the attention work of a native 64-wide kernel, but on the tensor cores and without a second code path.
+        qp, kp, vp = (F.pad(t, (0, 64)) for t in (q, k, v))
+        return attention(qp, kp, vp, causal=causal, scale=scale)[..., :64]
     if (causal and S % 128 and q.is_cuda and q.dtype == torch.bfloat16 and q.shape[-1] == 128
             and kernel_config().attention == "native" and native.has_symbol("llmctl_flash_attn_fwd")):
         # ragged length (every serving prefill): pad the sequence to the kernel's 128-token tile.  Under the causal
@@ -229,7 +236,12 @@ def rope_attention_packed(qkv: torch.Tensor, cos: torch.Tensor, sin: torch.Tenso
         use_native = _native_ok(v5[:, :, 0], v5[:, :, 1], v5[:, :, 2]) and \
             (native.has_symbol("llmctl_flash_attn_bwd") or not torch.is_grad_enabled())
         pos = None if positions is None else positions.to(torch.int32)
-        return _RopeAttnPackedFn.apply(qkv, cos, sin, batch, seq, heads, head_dim, pos, scale, use_native)
+        # shapes the kernel only takes after padding (head_dim 64, ragged length) go through the composed ops below,
+        # where attention() pads them, instead of dropping to the library inside the fused node
+        paddable = (not use_native and cfg.attention == "native" and native.has_symbol("llmctl_flash_attn_bwd")
+                    and (head_dim == 64 or (head_dim == 128 and seq % 128 != 0)))
+        if not paddable:
+            return _RopeAttnPackedFn.apply(qkv, cos, sin, batch, seq, heads, head_dim, pos, scale, use_native)
     qkv = ops.rope_packed(qkv, cos, sin, 2 * heads, head_dim, seq, positions)
     v5 = qkv.view(batch, seq, 3, heads, head_dim)
     o = attention(v5[:, :, 0], v5[:, :, 1], v5[:, :, 2], causal=True, scale=scale)

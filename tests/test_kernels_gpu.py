@@ -300,3 +300,28 @@ def test_flash_attention_ragged_lengths_use_the_native_kernel(cuda_device, S):
     _close(o, ref, 2e-2, 2e-2, "out")
     for i, name in enumerate(("dq", "dk", "dv")):
         _close(qkv.grad[:, :, i], ref_in.grad[:, :, i], 4e-2, 4e-2, name)
+
+
+def test_flash_attention_head_dim_64_uses_the_native_kernel(cuda_device):
+    """head_dim 64 (gpt-125m): zero-padded to the kernel's 128-wide head, forward and backward vs the fp32 reference."""
+    from llmctl_b200.ops import attention as attn, native
+    if not native.has_symbol("llmctl_flash_attn_bwd"):
+        pytest.skip("flash attention kernels not built")
+    B, S, H, D = 2, 300, 6, 64
+    torch.manual_seed(13)
+    qkv = (0.5 * torch.randn(B, S, 3, H, D, device=cuda_device)).bfloat16().requires_grad_(True)
+    q, k, v = qkv[:, :, 0], qkv[:, :, 1], qkv[:, :, 2]
+    before = native.launch_count
+    o = attn.attention(q, k, v, causal=True)
+    assert native.launch_count > before and o.shape == (B, S, H, D)
+    do = torch.randn_like(o)
+    o.backward(do)
+    ref_in = qkv.detach().float().requires_grad_(True)
+    qf, kf, vf = (ref_in[:, :, i].transpose(1, 2) for i in range(3))
+    s = qf @ kf.transpose(-1, -2) / math.sqrt(D)
+    s = s.masked_fill(torch.triu(torch.ones(S, S, dtype=torch.bool, device=cuda_device), 1), float("-inf"))
+    ref = (torch.softmax(s, -1) @ vf).transpose(1, 2)
+    ref.backward(do.float())
+    _close(o, ref, 2e-2, 2e-2, "out")
+    for i, name in enumerate(("dq", "dk", "dv")):
+        _close(qkv.grad[:, :, i], ref_in.grad[:, :, i], 4e-2, 4e-2, name)
