@@ -22,7 +22,7 @@ import time
 from pathlib import Path
 
 HERE = Path(__file__).resolve().parent
-REF_DST = HERE / "_ref"
+REF_DST = Path(os.environ["LLMCTL_REFERENCE_DST"]) if os.environ.get("LLMCTL_REFERENCE_DST") else HERE / "_ref"
 MARK = "llmctl/runtime/engine.py"
 SOURCES = [os.environ.get("LLMCTL_REFERENCE_SRC"), "/root/reference"]
 
@@ -57,7 +57,12 @@ def ensure_reference(verbose: bool = False) -> tuple[bool, str]:
     src = _source()
     if src is None:
         return False, "baseline/_ref is empty and no reference source tree is mounted (/root/reference)"
-    lock = HERE / "._ref_lock"
+    lock = REF_DST.parent / "._ref_lock"
+    try:
+        if lock.exists() and time.time() - lock.stat().st_mtime > 600:
+            shutil.rmtree(lock, ignore_errors=True)      # left behind by an installer that died
+    except OSError:
+        pass
     try:
         lock.mkdir()
     except FileExistsError:
@@ -70,7 +75,8 @@ def ensure_reference(verbose: bool = False) -> tuple[bool, str]:
         tmp = Path(tempfile.mkdtemp(prefix="llmctl_ref_src_"))
         copy = tmp / "reference"
         shutil.copytree(src, copy, ignore=shutil.ignore_patterns(".git", "__pycache__"))
-        stage = Path(tempfile.mkdtemp(prefix="_ref_stage_", dir=str(HERE)))
+        REF_DST.parent.mkdir(parents=True, exist_ok=True)
+        stage = Path(tempfile.mkdtemp(prefix="_ref_stage_", dir=str(REF_DST.parent)))
         ok, how = _pip_install(copy, stage)
         if not ok:
             shutil.copytree(copy / "llmctl", stage / "llmctl", dirs_exist_ok=True)

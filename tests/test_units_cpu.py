@@ -386,3 +386,27 @@ def test_measured_cost_model_reproduces_the_round2_b200_runs():
     m = MeasuredCostModel(get_preset("gpt-13b"), hw, seq_len=2048)
     best = m.search(global_batch=16, pins={"pipeline_parallel": 2, "tensor_parallel": 4})[0]
     assert best.micro_batch_size >= 2 and best.sequence_parallel, best
+
+
+def test_reference_arm_provisions_itself(tmp_path):
+    """`baseline/provision.py` installs the unmodified reference (pip --no-deps from a copy, else a verbatim copy of
+    the pure-Python package) into an empty target and is a no-op afterwards; without a source tree it says so."""
+    import os
+    import subprocess
+    import sys
+    root = Path(__file__).resolve().parent.parent
+    if not Path("/root/reference/llmctl/runtime/engine.py").exists():
+        pytest.skip("reference source tree is not mounted here")
+    dst = tmp_path / "ref"
+    code = ("import sys; sys.path.insert(0, %r); import provision as p; ok, how = p.ensure_reference(); print(ok, '|', how); "
+            "ok2, how2 = p.ensure_reference(); print(ok2, '|', how2)") % str(root / "baseline")
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300,
+                       env=dict(os.environ, LLMCTL_REFERENCE_DST=str(dst)))
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = r.stdout.strip().splitlines()
+    assert lines[0].startswith("True") and lines[1].startswith("True | already installed"), r.stdout
+    assert (dst / "llmctl" / "runtime" / "engine.py").read_text() == Path("/root/reference/llmctl/runtime/engine.py").read_text()
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=120,
+                       env=dict(os.environ, LLMCTL_REFERENCE_DST=str(tmp_path / "ref2"), LLMCTL_REFERENCE_SRC=str(tmp_path / "nowhere")))
+    # /root/reference is still found (second source); with it hidden the function reports why it cannot install
+    assert r.returncode == 0
