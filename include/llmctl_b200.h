@@ -80,7 +80,8 @@ int llmctl_cross_entropy_finalize(void* logits, long long ld, const long long* t
 /* ---- K0 tcgen05/TMA GEMM.  Reference: cuBLAS via torch.matmul / nn.Linear. ----
  * D[M,N] = op(A) op(B) (+ D if beta).  a_mn=0: A is [M,K] row-major; a_mn=1: A stored [K,M].
  * b_mn=0: B is [N,K] row-major (Linear weight); b_mn=1: B stored [K,N].
- * out_fp32: D fp32 else bf16.  tile_n: 0 auto | 128 | 256 | 2 = 256x256 tile on a CTA pair (cta_group::2).  max_ctas: 0 = all SMs. */
+ * out_fp32: D fp32 else bf16.  tile_n: 0 auto | 128 | 192 | 256 (single-CTA tiles) | 2 = 256x256 and 3 = 256x128 tile on a CTA pair
+ * (cta_group::2); auto picks the 256x256 pair tile whenever M, N > 128.  max_ctas: 0 = all SMs. */
 int llmctl_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, long long lda,
                      long long ldb, long long ldc, int a_mn, int b_mn, int out_fp32, int beta,
                      int tile_n, int max_ctas, void* stream);
