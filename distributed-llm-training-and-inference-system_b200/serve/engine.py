@@ -370,16 +370,27 @@ class InferenceEngine:
             # fused TP path: every row-parallel partial product is reduced + normed by one K11 launch
             ar, eps = self._ar, self.cfg.layer_norm_eps
             ar.begin_step()
+            # row-parallel projections write their partial sums straight into the symmetric buffer; at decode batch
+            # sizes the weight-streaming (skinny) GEMM is the right kernel for them as well
+            from ..ops import native as _native
+            skinny = (B <= ops.SKINNY_MAX_ROWS and ops.kernel_config().skinny_gemm
+                      and _native.has_symbol("llmctl_gemm_skinny_bf16"))
+
+            def rowpar(a_, w_, out_):
+                # (K a multiple of the 64-deep k-block only: the K-tail of the skinny kernel is not covered by a test)
+                if skinny and w_.shape[1] % 64 == 0:
+                    return ops.gemm_skinny(a_, w_, out=out_)
+                return ops.gemm_raw(a_, w_, out=out_)
             x = x.reshape(B, -1)
             y, residual = m.blocks[0].norm1(x, None)
             for i, blk in enumerate(m.blocks):
                 qkv = self._rope(blk.attn.qkv(y), inp.positions)
                 a = attn(i, qkv)
-                ops.gemm_raw(a, blk.attn.out.weight, out=ar.partial_out(B))
+                rowpar(a, blk.attn.out.weight, ar.partial_out(B))
                 y, residual = ar.reduce_norm(B, residual, blk.norm2.weight, eps)
                 gu = blk.mlp.up(y)
                 act = ops.swiglu(gu) if blk.mlp.gated else F.gelu(gu)
-                ops.gemm_raw(act, blk.mlp.down.weight, out=ar.partial_out(B))
+                rowpar(act, blk.mlp.down.weight, ar.partial_out(B))
                 nxt = m.blocks[i + 1].norm1 if i + 1 < len(m.blocks) else m.final_norm
                 y, residual = ar.reduce_norm(B, residual, nxt.weight, eps)
             return m.lm_head(y) if m.lm_head is not None else ops.linear(y, m.embed.weight)
