@@ -377,8 +377,7 @@ class InferenceEngine:
                       and _native.has_symbol("llmctl_gemm_skinny_bf16"))
 
             def rowpar(a_, w_, out_):
-                # (K a multiple of the 64-deep k-block only: the K-tail of the skinny kernel is not covered by a test)
-                if skinny and w_.shape[1] % 64 == 0:
+                if skinny:
                     return ops.gemm_skinny(a_, w_, out=out_)
                 return ops.gemm_raw(a_, w_, out=out_)
             x = x.reshape(B, -1)

@@ -325,3 +325,18 @@ def test_flash_attention_head_dim_64_uses_the_native_kernel(cuda_device):
     _close(o, ref, 2e-2, 2e-2, "out")
     for i, name in enumerate(("dq", "dk", "dv")):
         _close(qkv.grad[:, :, i], ref_in.grad[:, :, i], 4e-2, 4e-2, name)
+
+
+@pytest.mark.parametrize("M,N,K", [(8, 4096, 1376), (8, 4096, 512), (5, 1000, 200), (32, 2752, 4096), (1, 4096, 1384)])
+def test_skinny_gemm_k_tail_and_odd_shapes(cuda_device, M, N, K):
+    """Decode GEMM on shapes whose K is not a multiple of the 64-deep k-block (GPT-7B down-projection at TP=8:
+    K = 1376) and on N that is not a multiple of the tile: vs fp32 matmul."""
+    from llmctl_b200.ops import functional as ops, native
+    if not native.has_symbol("llmctl_gemm_skinny_bf16"):
+        pytest.skip("skinny GEMM not built")
+    torch.manual_seed(0)
+    x = torch.randn(M, K, device=cuda_device).bfloat16()
+    w = (0.05 * torch.randn(N, K, device=cuda_device)).bfloat16()
+    y = ops.gemm_skinny(x, w)
+    ref = x.float() @ w.float().t()
+    assert ((y.float() - ref).abs().max() / ref.abs().max()).item() < 1e-2
