@@ -17,7 +17,7 @@ declared-but-unsupported with a pointer to the schemes above.
 """
 from __future__ import annotations
 
-from typing import Dict, Iterable
+from typing import Dict
 
 import torch
 
@@ -109,7 +109,3 @@ def dequantize_if_needed(sd: Dict[str, torch.Tensor], scheme: str | None, dtype:
 
 def relative_error(a: torch.Tensor, b: torch.Tensor) -> float:
     return float((a.float() - b.float()).norm() / a.float().norm().clamp_min(1e-12))
-
-
-def names(items: Iterable[str]) -> str:
-    return ", ".join(sorted(items))
