@@ -7,7 +7,7 @@ Two calibration-free round-to-nearest schemes are built in:
 
 Matrices (2-D weights of the linear layers) are quantised; embeddings, norms and anything 1-D stay in the source
 precision.  A quantised tensor ``name`` is stored as ``name`` (int8 / packed uint8) plus ``name.scale`` (fp16) and the
-scheme is recorded in the artifact's ``export.json``; ``dequantize_state_dict`` restores bf16 weights on load, so a
+scheme is recorded in the artifact's ``export.json``; ``dequantize_if_needed`` restores bf16 weights on load, so a
 quantised artifact is served by the same engine (weight bytes on disk shrink 2x / 4x).
 
 Reference: ``--quant int8-awq|int4-gptq`` is an option of a stub command (reference llmctl/cli/commands/export.py:17)
