@@ -60,6 +60,25 @@ def inspect(
                         row += [f"{x.mean():.4g}", f"{x.std():.4g}", f"{x.abs().max():.4g}"]
                     t.add_row(*row)
                     rows += 1
+    for f in sorted(ck.glob("*.gguf")):                    # llama.cpp containers written by `export --format gguf`
+        from ...io.gguf import read_gguf
+        meta, tensors = read_gguf(f)
+        console.print(f"{f.name}: GGUF v3, architecture {meta.get('general.architecture')}, "
+                      f"{meta.get('llama.block_count')} blocks, hidden {meta.get('llama.embedding_length')}, "
+                      f"vocabulary {meta.get('llama.vocab_size')}")
+        for k, tensor in tensors.items():
+            total += tensor.numel()
+            if rows < limit:
+                row = [f.name, k, str(tuple(tensor.shape)), str(tensor.dtype).replace("torch.", "")]
+                if stats:
+                    x = tensor.float()
+                    row += [f"{x.mean():.4g}", f"{x.std():.4g}", f"{x.abs().max():.4g}"]
+                t.add_row(*row)
+                rows += 1
+    exp = ck / "export.json"
+    if exp.exists():
+        info = json.loads(exp.read_text())
+        console.print(f"export: format {info.get('format')}, quantization {info.get('quantization') or 'none'}")
     console.print(t)
     console.print(f"[green]{total:,} parameters in weight files[/green]")
     return total

@@ -115,6 +115,8 @@ def test_train_eval_export_inspect_gc_replay(tmp_path):
     assert r.returncode != 0 and "unsupported" in (r.stdout + r.stderr)
     r = run("export", "convert", "--ckpt", str(out / "final"), "--format", "gguf", "--out", str(tmp_path / "art_gguf"))
     assert r.returncode == 0 and (tmp_path / "art_gguf" / "model.gguf").exists(), r.stdout + r.stderr
+    r = run("admin", "inspect", "--checkpoint", str(tmp_path / "art_gguf"))
+    assert r.returncode == 0 and "GGUF v3" in r.stdout and "token_embd.weight" in r.stdout, r.stdout + r.stderr
     r = run("export", "convert", "--ckpt", str(out / "final"), "--quant", "int8", "--out", str(tmp_path / "art_q"))
     assert r.returncode == 0 and json.loads((tmp_path / "art_q" / "export.json").read_text())["quantization"] == "int8"
     r = run("export", "convert", "--ckpt", str(out / "final"), "--quant", "int4-gptq", "--out", str(tmp_path / "art_q2"))
