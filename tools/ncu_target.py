@@ -18,6 +18,12 @@ elif what == "gemm_wgrad":  # both operands MN-major
     dy = torch.randn(4096, 12288, device=dev).bfloat16(); x = torch.randn(4096, 4096, device=dev).bfloat16()
     for _ in range(6):
         ops.gemm_raw(dy, x, a_mn=True, b_mn=True)
+elif what == "gemm_tp8":    # short-K row-parallel shapes of a TP=8 shard: out-proj (K=512) and down-proj (K=1376)
+    x1 = torch.randn(4096, 512, device=dev).bfloat16(); w1 = torch.randn(4096, 512, device=dev).bfloat16()
+    x2 = torch.randn(4096, 1376, device=dev).bfloat16(); w2 = torch.randn(4096, 1376, device=dev).bfloat16()
+    for _ in range(3):
+        ops.gemm_raw(x1, w1)
+        ops.gemm_raw(x2, w2)
 elif what == "gemm1":       # single-CTA 128x256 tile kernel
     a = torch.randn(4096, 4096, device=dev).bfloat16(); b = torch.randn(12288, 4096, device=dev).bfloat16()
     for _ in range(6):
