@@ -126,7 +126,8 @@ int llmctl_flash_attn_bwd(const void* q, const void* k, const void* v, const voi
                           int D, long long q_tok_stride, long long k_tok_stride, long long v_tok_stride,
                           long long o_tok_stride, long long dqkv_tok_stride, float scale, int causal, void* stream);
 /* In-kernel timeline of the forward's CTA 0 (only recorded when LLMCTL_FLASH_TRACE is set in the environment):
- * copies up to 2048 (clock64, event) words to host_out; read with tools/trace_flash.py.  Returns the count or < 0. */
+ * copies the 2048-word (clock64, event) log to host_out (synchronous); read with tools/trace_flash.py.  Returns a
+ * cudaError_t value: 0 = ok, cudaErrorNotReady when tracing is off. */
 int llmctl_flash_trace_read(long long* host_out);
 
 /* ---- Peer-memory (NVLink 5 / NVSwitch) kernels.  No counterpart in the reference (llmctl/comms is empty).
