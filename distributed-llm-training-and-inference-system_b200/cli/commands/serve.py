@@ -25,6 +25,7 @@ def start(
     max_batch_tokens: int = typer.Option(8192, "--max-batch-tokens"),
     max_concurrent: int = typer.Option(128, "--max-concurrent"),
     device: str = typer.Option("auto", "--device", help="auto | cuda | cpu"),
+    tensor_parallel: int = typer.Option(1, "--tensor-parallel", "--tp", help="Shard the model over this many GPUs (one process per GPU, rank 0 serves HTTP)"),
     dry_run: bool = typer.Option(False, "--dry-run", help="Validate and print the configuration, do not serve"),
 ):
     """Start the paged-attention, continuous-batching inference server."""
@@ -41,6 +42,24 @@ def start(
     console.print(f"[bold blue]Starting inference server[/bold blue]  artifact={artifact} {host}:{port} "
                   f"scheduler={scheduler} max_batch_size={max_batch_size} max_batch_tokens={max_batch_tokens} "
                   f"max_concurrent={max_concurrent} device={device}")
+    if tensor_parallel > 1:
+        # one process per GPU under torchrun: rank 0 runs the HTTP server, the others mirror its engine step by step
+        import subprocess
+        import sys
+        from ...runtime.launcher import free_port
+        worker = str(Path(__file__).resolve().parents[2] / "serve" / "tp_worker.py")
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={tensor_parallel}",
+               "--master-addr", "127.0.0.1", "--master-port", str(free_port()), worker, "--artifact", str(artifact),
+               "--host", host, "--port", str(port), "--scheduler", scheduler, "--max-batch-size", str(max_batch_size),
+               "--max-batch-tokens", str(max_batch_tokens), "--max-concurrent", str(max_concurrent), "--device", device]
+        if dry_run:
+            console.print("[yellow]Dry run: configuration valid.[/yellow] " + " ".join(cmd))
+            return cfg
+        try:
+            return subprocess.call(cmd)
+        except KeyboardInterrupt:
+            console.print("[yellow]Server stopped.[/yellow]")
+            return 0
     if dry_run:
         console.print("[yellow]Dry run: configuration valid.[/yellow]")
         return cfg

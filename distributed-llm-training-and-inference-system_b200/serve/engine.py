@@ -77,6 +77,7 @@ class Sequence:
     first_token_time: Optional[float] = None
     on_token: Optional[object] = None      # callback(seq, token) for streaming
     cancel_requested: bool = False         # set from any thread (client went away); honoured at the next token
+    cancel_applied: bool = False           # lockstep (TP) serving: the cancellation has reached every rank
     done_event: threading.Event = field(default_factory=threading.Event)
 
     @property
@@ -208,6 +209,7 @@ class InferenceEngine:
                  cuda_graphs: Optional[bool] = None, fused_tp_decode: Optional[bool] = None):
         self.model, self.cfg, self.tokenizer, self.device = load_model_for_inference(artifact, device)
         self.st = get_state()
+        self.lockstep = False       # True under serve/lockstep.py: cancellations take effect on all TP ranks at once
         m = self.model
         self.heads_local = m.blocks[0].attn.heads_local
         self.head_dim = self.cfg.head_dim
@@ -520,7 +522,7 @@ class InferenceEngine:
             except Exception:  # noqa: BLE001 - a broken stream consumer must not kill the engine
                 pass
         eos = getattr(self.tokenizer, "eos_token_id", None)
-        if s.cancel_requested:
+        if (s.cancel_applied if self.lockstep else s.cancel_requested):
             s.finish_reason = "cancelled"          # frees the KV blocks and the batch slot right away
         elif eos is not None and tok == eos:
             s.finish_reason = "stop"

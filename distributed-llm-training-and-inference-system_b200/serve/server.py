@@ -66,7 +66,8 @@ class EngineLoop(threading.Thread):
             if not self.engine.has_work():
                 self.wake.wait(timeout=0.05)
                 self.wake.clear()
-                continue
+                if not self.engine.has_work():
+                    continue
             try:
                 done = self.engine.step()
                 if self.on_finished:
@@ -100,6 +101,8 @@ class InferenceServer:
         self.errors = 0
         self.loop_thread = EngineLoop(self.engine)
         self.loop_thread.on_finished = self._record
+        if hasattr(self.engine, "on_pending"):            # tensor-parallel serving (serve/lockstep.py)
+            self.engine.on_pending = self.loop_thread.wake.set
         try:
             # register the llmctl_inference_* metrics in the default registry: GET /metrics serves them from this
             # process, no second HTTP server is started
@@ -171,9 +174,10 @@ class InferenceServer:
                                          "total_tokens": n_prompt + len(seq.generated)})
 
     async def handle_generation_request(self, req: GenerationRequest) -> GenerationResponse:
-        rid, seq, n_prompt = self._submit(req)
+        loop = asyncio.get_running_loop()
+        # off the event loop: under tensor-parallel (lockstep) serving admission waits for the next engine step
+        rid, seq, n_prompt = await loop.run_in_executor(None, self._submit, req)
         try:
-            loop = asyncio.get_running_loop()
             await loop.run_in_executor(None, seq.done_event.wait)
             self.completed += 1
             if seq.finish_reason == "error":
@@ -191,7 +195,7 @@ class InferenceServer:
         def on_token(seq, tok):
             loop.call_soon_threadsafe(q.put_nowait, tok)
 
-        rid, seq, n_prompt = self._submit(req, on_token=on_token)
+        rid, seq, n_prompt = await loop.run_in_executor(None, self._submit, req, on_token)
         try:
             sent = 0
             while True:
@@ -238,6 +242,9 @@ class InferenceServer:
 
     def shutdown(self):
         self.loop_thread.stop()
+        if hasattr(self.engine, "stop"):                  # lockstep leader: release the follower ranks
+            self.loop_thread.join(timeout=5.0)
+            self.engine.stop()
 
 
 def create_inference_server(model_path: str, **kwargs) -> InferenceServer:

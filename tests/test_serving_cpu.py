@@ -219,3 +219,65 @@ def test_cancelled_sequence_frees_its_blocks_early():
     assert a.finished and a.finish_reason == "cancelled" and len(a.generated) < 10
     assert b.finish_reason == "length" and len(b.generated) == 6
     assert eng.kv.free_blocks == 64 and steps < 12
+
+
+def test_tensor_parallel_http_serving_lockstep(tmp_path):
+    """`llmctl serve --tensor-parallel 2` on CPU/gloo: two processes, each with half of every weight matrix; rank 0
+    answers HTTP, the follower mirrors its engine step by step (serve/lockstep.py).  Concurrent completions finish with
+    the requested number of tokens, a greedy request is reproducible, /health reports the shared KV pool."""
+    import os
+    import subprocess
+    import sys
+    import time
+    import urllib.request
+    from pathlib import Path
+    from dist_utils import free_port
+    root = Path(__file__).resolve().parent.parent
+    port = free_port()
+    worker = root / "distributed-llm-training-and-inference-system_b200" / "serve" / "tp_worker.py"
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", str(free_port()), str(worker), "--artifact", "gpt-tiny", "--host", "127.0.0.1", "--port", str(port),
+           "--device", "cpu", "--max-batch-size", "4", "--num-kv-blocks", "256"]
+    proc = subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True,
+                            env=dict(os.environ, PYTHONPATH=str(root), OMP_NUM_THREADS="2"), start_new_session=True)
+
+    def post(payload, timeout=120):
+        req = urllib.request.Request(f"http://127.0.0.1:{port}/v1/completions", data=json.dumps(payload).encode(),
+                                     headers={"Content-Type": "application/json"})
+        with urllib.request.urlopen(req, timeout=timeout) as r:
+            return json.loads(r.read())
+    try:
+        deadline = time.time() + 120
+        while True:
+            try:
+                with urllib.request.urlopen(f"http://127.0.0.1:{port}/health", timeout=2) as r:
+                    health = json.loads(r.read())
+                break
+            except Exception:  # noqa: BLE001 - not up yet
+                assert proc.poll() is None, proc.stdout.read()[-3000:]
+                assert time.time() < deadline, "server did not come up"
+                time.sleep(0.5)
+        assert health["status"] == "healthy" and health["kv_total_blocks"] == 256
+        import concurrent.futures as cf
+        with cf.ThreadPoolExecutor(4) as ex:
+            futs = [ex.submit(post, {"prompt": f"hello {i}", "max_tokens": 6 + i, "temperature": 0.0}) for i in range(4)]
+            outs = [f.result() for f in futs]
+        for i, o in enumerate(outs):
+            assert o["finish_reason"] in ("length", "stop") and o["usage"]["completion_tokens"] <= 6 + i
+            assert o["usage"]["completion_tokens"] >= 1
+        a = post({"prompt": "the same prompt", "max_tokens": 8, "temperature": 0.0})
+        b = post({"prompt": "the same prompt", "max_tokens": 8, "temperature": 0.0})
+        assert a["text"] == b["text"] and a["usage"] == b["usage"]
+        with urllib.request.urlopen(f"http://127.0.0.1:{port}/health", timeout=5) as r:
+            h2 = json.loads(r.read())
+        assert h2["kv_free_blocks"] == 256 and h2["active_requests"] == 0          # every block returned on every step
+    finally:
+        import signal
+        try:
+            os.killpg(proc.pid, signal.SIGTERM)
+        except ProcessLookupError:
+            pass
+        try:
+            proc.wait(timeout=20)
+        except subprocess.TimeoutExpired:
+            os.killpg(proc.pid, signal.SIGKILL)
