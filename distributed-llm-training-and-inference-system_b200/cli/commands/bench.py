@@ -185,7 +185,8 @@ def e2e(
         threading.Timer(30.0, lambda: os._exit(0)).start()
         del eng
         gc.collect()
-        torch.cuda.synchronize()
+        if torch.cuda.is_available():
+            torch.cuda.synchronize()
         dist.barrier()
         dist.destroy_process_group()
         os._exit(0)

@@ -281,3 +281,23 @@ def test_tensor_parallel_http_serving_lockstep(tmp_path):
             proc.wait(timeout=20)
         except subprocess.TimeoutExpired:
             os.killpg(proc.pid, signal.SIGKILL)
+
+
+def test_bench_e2e_tensor_parallel_cli_on_gloo():
+    """`llmctl bench e2e --tp 2` under torchrun on CPU/gloo: the serving benchmark's tensor-parallel path (mesh set-up,
+    identical admission on both ranks, orderly teardown) — rank 0 prints the result."""
+    import os
+    import subprocess
+    import sys
+    from pathlib import Path
+    from dist_utils import free_port
+    root = Path(__file__).resolve().parent.parent
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", str(free_port()), "-m", "llmctl_b200.cli.main", "bench", "e2e", "--tp", "2", "--model", "gpt-tiny",
+           "--prompt-length", "16", "--gen-length", "4", "--num-requests", "2", "--warmup-runs", "0"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, cwd=str(root),
+                       env=dict(os.environ, PYTHONPATH=str(root), OMP_NUM_THREADS="2"))
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    out = r.stdout
+    res = json.loads(out[out.index("{"):out.rindex("}") + 1])
+    assert res["tensor_parallel"] == 2 and res["steps"] == 4 and res["decode_tokens_per_s"] > 0
