@@ -18,6 +18,7 @@ class TrainingTracker:
         self.tokens_per_step = tokens_per_step
         cfg = engine.model_config
         self.flops_per_token = cfg.flops_per_token(engine.config.seq_len) if cfg is not None else 0.0
+        self.hbm_bytes_per_step, self.nvlink_bytes_per_step = self._traffic_model()
         self._obs = None
         self._health = None
         try:
@@ -39,6 +40,36 @@ class TrainingTracker:
         except Exception:  # noqa: BLE001
             self._health = None
 
+    def _traffic_model(self):
+        """Bytes one GPU moves per optimizer step, from the run's configuration (estimates, labelled as such in the
+        log): HBM = weights read by forward / dgrad / wgrad of every micro-batch + the AdamW pass over this rank's
+        optimizer shard; NVLink = ZeRO gradient / parameter traffic + TP/SP all-gather / reduce-scatter + PP sends.
+        These feed the `mem_bw` / `comm_bw` telemetry names the reference declares and never computes (reference
+        llmctl/cli/commands/init.py:155) and the step's roofline fraction (metrics/roofline.py)."""
+        e = self.engine
+        cfg, c, st = e.model_config, e.config, e.state
+        if cfg is None:
+            return 0.0, 0.0
+        P = cfg.num_parameters() / max(st.tp * st.pp, 1)
+        n_micro = max(c.gradient_accumulation_steps, 1)
+        zero = getattr(c, "zero_stage", 0) or 0
+        shard = st.dp if (zero >= 1 and st.dp > 1) else 1
+        hbm = 3 * 2.0 * P * n_micro + 28.0 * P / shard + 2 * 2.0 * P        # weight reads, AdamW, gradient write + read
+        link = 0.0
+        if st.dp > 1:
+            f = (st.dp - 1) / st.dp
+            link += 2.0 * P * f * (2.0 if zero == 0 else 1.0) * (n_micro if zero >= 2 else 1)
+            if zero >= 1:
+                link += 2.0 * P * f * ((2.0 * n_micro + 1.0) if zero >= 3 else 1.0)
+        tokens = c.batch_size * c.seq_len
+        layers = max(cfg.layers // max(st.pp, 1), 1)
+        if st.tp > 1:
+            per = tokens * cfg.hidden * 2.0 * (st.tp - 1) / st.tp
+            link += 8 * layers * per * n_micro * (1.0 if st.sequence_parallel else 2.0)
+        if st.pp > 1:
+            link += 2 * n_micro * tokens * cfg.hidden * 2.0 / (st.tp if st.sequence_parallel else 1)
+        return hbm, link
+
     def log(self, step: int, loss: float, grad_norm: float, lr: float, step_time: float) -> Dict[str, Any]:
         e = self.engine
         tps = self.tokens_per_step / step_time if step_time > 0 else 0.0
@@ -48,6 +79,12 @@ class TrainingTracker:
         mfu = flops / (peak_flops() * world) if e.state.device.type == "cuda" else 0.0
         rec = {"step": step, "loss": loss, "grad_norm": grad_norm, "lr": lr, "step_time_s": step_time,
                "tokens_per_s": tps, "flops": flops, "mfu": mfu, "time": time.time()}
+        if step_time > 0:
+            from .roofline import RooflinePoint
+            rp = RooflinePoint("train_step", step_time, flops=flops * step_time / max(world, 1),
+                               hbm_bytes=self.hbm_bytes_per_step, nvlink_bytes=self.nvlink_bytes_per_step).report(sustained=True)
+            rec.update(mem_bw_gbs_est=rp["achieved_hbm_gbs"], comm_bw_gbs_est=rp["achieved_nvlink_gbs"],
+                       roofline_bound=rp["bound"], roofline_fraction=rp["fraction_of_roofline"])
         if e.is_main:
             e.logger.info("step %d loss %.4f grad_norm %.3f lr %.3e %.1f ms/step %.0f tok/s MFU %.1f%%",
                           step, loss, grad_norm, lr, step_time * 1e3, tps, mfu * 100)

@@ -103,6 +103,8 @@ def test_train_eval_export_inspect_gc_replay(tmp_path):
     assert (out / "final" / "model.safetensors").exists() and (out / "final" / "training_state.json").exists()
     st = json.loads((out / "final" / "training_state.json").read_text())
     assert st["global_step"] == 6 and st["config"]["seed"] == 7
+    rec = json.loads((out / "metrics.jsonl").read_text().strip().splitlines()[-1])     # telemetry names of the preset
+    assert {"loss", "grad_norm", "tokens_per_s", "flops", "mfu", "mem_bw_gbs_est", "comm_bw_gbs_est", "roofline_fraction"} <= set(rec)
     r = run("eval", "run", "--ckpt", str(out / "final"), "--tasks", "perplexity,accuracy,latency", "--out", str(tmp_path / "eval.json"),
             "--batches", "2", "--seq-len", "32")
     assert r.returncode == 0, r.stdout + r.stderr
