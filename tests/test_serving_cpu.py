@@ -268,9 +268,27 @@ def test_tensor_parallel_http_serving_lockstep(tmp_path):
         a = post({"prompt": "the same prompt", "max_tokens": 8, "temperature": 0.0})
         b = post({"prompt": "the same prompt", "max_tokens": 8, "temperature": 0.0})
         assert a["text"] == b["text"] and a["usage"] == b["usage"]
-        with urllib.request.urlopen(f"http://127.0.0.1:{port}/health", timeout=5) as r:
-            h2 = json.loads(r.read())
-        assert h2["kv_free_blocks"] == 256 and h2["active_requests"] == 0          # every block returned on every step
+        # a streaming client that goes away after the first event: the cancellation must reach the follower too, or the
+        # two ranks would disagree about the batch from the next step on and the following request could not complete
+        import socket
+        body = json.dumps({"prompt": "abandoned", "max_tokens": 200, "temperature": 0.0, "stream": True}).encode()
+        sk = socket.create_connection(("127.0.0.1", port), timeout=30)
+        sk.sendall(b"POST /v1/completions HTTP/1.1\r\nHost: x\r\nContent-Type: application/json\r\nContent-Length: "
+                   + str(len(body)).encode() + b"\r\n\r\n" + body)
+        got = b""
+        while b"data:" not in got:
+            got += sk.recv(4096)
+        sk.close()
+        c = post({"prompt": "after the cancel", "max_tokens": 5, "temperature": 0.0})
+        assert c["usage"]["completion_tokens"] >= 1
+        deadline = time.time() + 30
+        while True:
+            with urllib.request.urlopen(f"http://127.0.0.1:{port}/health", timeout=5) as r:
+                h2 = json.loads(r.read())
+            if h2["kv_free_blocks"] == 256 and h2["active_requests"] == 0:          # every block returned, also the abandoned one's
+                break
+            assert time.time() < deadline, h2
+            time.sleep(0.2)
     finally:
         import signal
         try:
